@@ -1,0 +1,584 @@
+// tcgen05 / TMEM / TMA GEMM and implicit-GEMM convolution for sm_100a.
+//
+// One persistent, warp-specialised kernel family covers every GEMM-shaped op of the framework:
+//   * Linear fwd / dgrad / wgrad        (replaces nn.Linear + BLAS sgemm: reference
+//                                        pytorch_code/model_ops/lenet.py:45-46, resnet.py:78;
+//                                        MPI_code/src/util/util.h:35-81 cblas_dgemm NN/NT/TN)
+//   * 3x3 stride-1 conv fprop / dgrad   (implicit GEMM, activation tiles fetched by *tiled* 4-D TMA
+//                                        with out-of-bounds zero fill acting as the padding;
+//                                        reference resnet.py:19-21, resnet_split.py:28,34)
+//   * 3x3 stride-1 conv wgrad           (split-K over pixels, MN-major operands, fp32 red.add
+//                                        epilogue straight into the flat gradient bucket)
+//   * im2col-lowered convs (stride 2, 1x1, stems) as plain GEMMs.
+//
+// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane issues
+// tcgen05.mma), warp 2 = TMEM allocator, warps 4-7 = epilogue (tcgen05.ld -> registers -> global).
+// Pipelines: smem ring full/empty (TMA <-> MMA), TMEM double buffer full/empty (MMA <-> epilogue),
+// static persistent tile scheduler.
+#include "common.cuh"
+#include "../include/pdnn_b200.h"
+
+#include <mutex>
+
+namespace pdnn {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 256;
+
+enum OperMode : int { OP_K2D = 0, OP_MN2D = 1, OP_CONVK = 2, OP_CONVMN = 3 };
+
+struct GemmParams {
+    int M, N, K;
+    int m_tiles, n_tiles, k_splits;
+    int k_iters_total, k_iters_per_split;
+    // geometry of the activation operand in the conv modes
+    int H, W, C, R, S, pad;
+    int box_h, box_n;        // pixel box (box_w == W)
+    int cblks;               // C / 64 (OP_CONVK) or C / BN (OP_CONVMN)
+    // epilogue
+    void* out;
+    long long ldo;           // row stride of out, in elements
+    int out_mode;            // 0: bf16 store, 1: fp32 store, 2: fp32 red.add (split-K / accumulate)
+    int relu;
+    float alpha;
+    const float* bias;       // per output column, may be null
+    const __nv_bfloat16* residual;  // optional bf16 [M][ldo] added before relu (bf16 out only)
+    // straggler abort guard: if *guard_closed >= *guard_step the kernel returns immediately
+    const uint32_t* guard_closed;
+    const uint32_t* guard_step;
+};
+
+template <int BN>
+struct SmemLayout {
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KiB
+    static constexpr int B_BYTES = BN * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BN <= 64) ? 8 : (BN <= 128 ? 6 : 4);
+    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
+};
+
+template <int AMODE, int BMODE, int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+    using L = SmemLayout<BN>;
+    constexpr int STAGES = L::STAGES;
+    constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+
+    if (p.guard_closed != nullptr) {
+        // one thread samples the guard so that the whole CTA takes the same branch
+        __shared__ int s_abort;
+        if (threadIdx.x == 0) s_abort = ld_relaxed_sys(p.guard_closed) >= ld_relaxed_sys(p.guard_step);
+        __syncthreads();
+        if (s_abort) return;
+    }
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t smem_base = smem_u32(smem);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+    const uint32_t bar_base = smem_u32(bars);
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull_bar(a), 1);
+            mbar_init(tempty_bar(a), 4);
+        }
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int total_tiles = p.m_tiles * p.n_tiles * p.k_splits;
+    const int hw = p.H * p.W;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int ks = tile % p.k_splits;
+                const int rest = tile / p.k_splits;
+                const int nt = rest % p.n_tiles;
+                const int mt = rest / p.n_tiles;
+                const int k_begin = ks * p.k_iters_per_split;
+                const int k_end = min(k_begin + p.k_iters_per_split, p.k_iters_total);
+                // per-tile constants of the conv modes
+                int a_n0 = 0, a_h0 = 0;
+                if (AMODE == OP_CONVK) {
+                    const int p0 = mt * BLOCK_M;
+                    a_n0 = p0 / hw;
+                    a_h0 = (p0 - a_n0 * hw) / p.W;
+                }
+                int b_r = 0, b_s = 0, b_c0 = 0;
+                if (BMODE == OP_CONVMN) {
+                    const int rs = nt / p.cblks;
+                    b_r = rs / p.S;
+                    b_s = rs - b_r * p.S;
+                    b_c0 = (nt - rs * p.cblks) * BN;
+                }
+                for (int kit = k_begin; kit < k_end; ++kit) {
+                    mbar_wait(empty_bar(stage), phase ^ 1);
+                    const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
+                    const uint32_t sb = sa + L::A_BYTES;
+                    const uint32_t fb = full_bar(stage);
+                    mbar_expect_tx(fb, L::STAGE_BYTES);
+                    // ---- A ----
+                    if (AMODE == OP_K2D) {
+                        tma_load_2d(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
+                    } else if (AMODE == OP_MN2D) {
+                        tma_load_2d(sa, &tmA, fb, mt * BLOCK_M, kit * BLOCK_K);
+                        tma_load_2d(sa + 8192, &tmA, fb, mt * BLOCK_M + 64, kit * BLOCK_K);
+                    } else if (AMODE == OP_CONVK) {
+                        const int rs = kit / p.cblks;
+                        const int cb = kit - rs * p.cblks;
+                        const int r = rs / p.S;
+                        const int s = rs - r * p.S;
+                        tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 + r - p.pad, a_n0);
+                    }
+                    // ---- B ----
+                    if (BMODE == OP_K2D) {
+                        tma_load_2d(sb, &tmB, fb, kit * BLOCK_K, nt * BN);
+                    } else if (BMODE == OP_MN2D) {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sb + j * 8192, &tmB, fb, nt * BN + j * 64, kit * BLOCK_K);
+                    } else if (BMODE == OP_CONVMN) {
+                        const int p0 = kit * BLOCK_K;   // 64 pixels per k-iteration
+                        const int n0 = p0 / hw;
+                        const int h0 = (p0 - n0 * hw) / p.W;
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_4d(sb + j * 8192, &tmB, fb, b_c0 + j * 64, b_s - p.pad,
+                                        h0 + b_r - p.pad, n0);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        constexpr uint32_t A_MN = (AMODE == OP_MN2D) ? 1u : 0u;
+        constexpr uint32_t B_MN = (BMODE == OP_MN2D || BMODE == OP_CONVMN) ? 1u : 0u;
+        constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+        int stage = 0;
+        uint32_t phase = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int ks = tile % p.k_splits;
+            const int k_begin = ks * p.k_iters_per_split;
+            const int k_end = min(k_begin + p.k_iters_per_split, p.k_iters_total);
+            mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * BN;
+            for (int kit = k_begin; kit < k_end; ++kit) {
+                mbar_wait(full_bar(stage), phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
+                    const uint32_t sb = sa + L::A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        // K-major: advance 32 bytes inside the 128B swizzle row; SBO = 8 rows * 128 B.
+                        // MN-major: advance 16 K-rows (2048 B); SBO = 8 K-rows (1024 B); LBO = next
+                        // 64-wide MN chunk (8192 B).
+                        const uint64_t adesc = A_MN ? make_smem_desc_sw128(sa + k * 2048, 8192, 1024)
+                                                    : make_smem_desc_sw128(sa + k * 32, 16, 1024);
+                        const uint64_t bdesc = B_MN ? make_smem_desc_sw128(sb + k * 2048, 8192, 1024)
+                                                    : make_smem_desc_sw128(sb + k * 32, 16, 1024);
+                        umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar(stage));
+                    if (kit == k_end - 1) umma_commit(tfull_bar(acc));
+                }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue =====================
+        const int ew = warp & 3;           // TMEM lane quarter this warp may touch
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int rest = tile / p.k_splits;
+            const int nt = rest % p.n_tiles;
+            const int mt = rest / p.n_tiles;
+            mbar_wait(tfull_bar(acc), acc_phase);
+            tc_fence_after();
+            const long long row = (long long)mt * BLOCK_M + ew * 32 + lane;
+            const bool row_ok = row < p.M;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + acc * BN + c * 32, v);
+                tmem_ld_wait();
+                const int col0 = nt * BN + c * 32;
+                if (!row_ok || col0 >= p.N) continue;
+                float f[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
+                const bool full = (col0 + 32 <= p.N);
+                if (p.bias != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (full || col0 + i < p.N) f[i] += __ldg(p.bias + col0 + i);
+                }
+                if (p.out_mode == 0) {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ldo + col0;
+                    const bool vec = full && ((p.ldo & 7) == 0);
+                    if (p.residual != nullptr) {
+                        const __nv_bfloat16* rp = p.residual + row * p.ldo + col0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (full || col0 + i < p.N) f[i] += __bfloat162float(rp[i]);
+                    }
+                    if (p.relu) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+                    }
+                    if (vec) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 w;
+                            w.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
+                            w.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
+                            w.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
+                            w.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
+                            *reinterpret_cast<uint4*>(o + q * 8) = w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (col0 + i < p.N) o[i] = __float2bfloat16(f[i]);
+                    }
+                } else {
+                    float* o = reinterpret_cast<float*>(p.out) + row * p.ldo + col0;
+                    if (p.relu) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+                    }
+                    const bool vec = full && ((p.ldo & 3) == 0);
+                    if (p.out_mode == 1) {
+                        if (vec) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                *reinterpret_cast<float4*>(o + q * 4) =
+                                    make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (col0 + i < p.N) o[i] = f[i];
+                        }
+                    } else {
+                        if (vec) {
+#pragma unroll
+                            for (int q = 0; q < 8; ++q)
+                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + q * 4),
+                                             "f"(f[q * 4]), "f"(f[q * 4 + 1]), "f"(f[q * 4 + 2]),
+                                             "f"(f[q * 4 + 3])
+                                             : "memory");
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (col0 + i < p.N) atomicAdd(o + i, f[i]);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    });
+    return fn;
+}
+
+// bf16 tensor map, up to 4 dims, dims[0] innermost (contiguous). strides in elements for dims 1..rank-1.
+static int make_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const long long* dims,
+                          const long long* strides_elems, const int* box) {
+    EncodeTiledFn enc = get_encode_fn();
+    PDNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t gdim[5];
+    cuuint64_t gstr[4];
+    cuuint32_t bdim[5];
+    cuuint32_t estr[5];
+    for (int i = 0; i < rank; ++i) {
+        gdim[i] = (cuuint64_t)dims[i];
+        bdim[i] = (cuuint32_t)box[i];
+        estr[i] = 1;
+        if (i > 0) gstr[i - 1] = (cuuint64_t)strides_elems[i] * 2ull;
+    }
+    PDNN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base pointer must be 16-byte aligned");
+    for (int i = 1; i < rank; ++i)
+        PDNN_REQUIRE((gstr[i - 1] & 15) == 0, "TMA stride of dim %d (%llu bytes) is not a multiple of 16", i,
+                     (unsigned long long)gstr[i - 1]);
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr,
+                     bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    PDNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rank %d)", (int)r, rank);
+    return 0;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+    if (g_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+
+template <int AMODE, int BMODE, int BN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
+                       cudaStream_t stream) {
+    using L = SmemLayout<BN>;
+    auto kern = gemm_tcgen05_kernel<AMODE, BMODE, BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+        attr_set = true;
+    }
+    const int total = p.m_tiles * p.n_tiles * p.k_splits;
+    int grid = total < num_sms() ? total : num_sms();
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(tmA, tmB, p);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+template <int AMODE, int BMODE>
+static int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
+                       cudaStream_t stream) {
+    switch (bn) {
+        case 64: return launch_gemm<AMODE, BMODE, 64>(tmA, tmB, p, max_ctas, stream);
+        case 128: return launch_gemm<AMODE, BMODE, 128>(tmA, tmB, p, max_ctas, stream);
+        case 256: return launch_gemm<AMODE, BMODE, 256>(tmA, tmB, p, max_ctas, stream);
+        default: pdnn_set_error("unsupported BLOCK_N %d", bn); return -2;
+    }
+}
+
+static int pick_bn(int N) {
+    if (N <= 64) return 64;
+    if (N <= 128) return 128;
+    if (N % 256 == 0) return 256;
+    if (N % 128 == 0) return 128;
+    return N >= 512 ? 256 : 128;
+}
+
+static void fill_epilogue(GemmParams& p, const pdnn_epilogue_t* epi) {
+    p.out = epi->out;
+    p.ldo = epi->ldo;
+    p.out_mode = epi->out_mode;
+    p.relu = epi->relu;
+    p.alpha = epi->alpha;
+    p.bias = epi->bias;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
+    p.guard_closed = epi->guard_closed;
+    p.guard_step = epi->guard_step;
+}
+
+static int choose_splits(int tiles_mn, int k_iters, int requested) {
+    if (requested > 0) return requested > k_iters ? k_iters : requested;
+    const int sms = num_sms();
+    if (tiles_mn >= sms || k_iters < 8) return 1;
+    int s = (sms + tiles_mn - 1) / tiles_mn;
+    if (s > k_iters / 4) s = k_iters / 4;
+    return s < 1 ? 1 : s;
+}
+
+static void finish_splits(GemmParams& p) {
+    p.k_iters_per_split = (p.k_iters_total + p.k_splits - 1) / p.k_splits;
+    p.k_splits = (p.k_iters_total + p.k_iters_per_split - 1) / p.k_iters_per_split;   // no empty split
+}
+
+}  // namespace pdnn
+
+using namespace pdnn;
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
+                              long long ldb, int M, int N, int K, const pdnn_epilogue_t* epi, int k_splits,
+                              void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+    PDNN_REQUIRE(epi != nullptr && epi->out != nullptr, "gemm: missing epilogue / output");
+    const int bn = pick_bn(N);
+    CUtensorMap tmA, tmB;
+    {
+        long long dims[2], str[2];
+        int box[2];
+        if (!a_mn_major) { dims[0] = K; dims[1] = M; str[1] = lda; box[0] = 64; box[1] = BLOCK_M; }
+        else             { dims[0] = M; dims[1] = K; str[1] = lda; box[0] = 64; box[1] = 64; }
+        str[0] = 1;
+        if (int rc = make_tmap_bf16(&tmA, A, 2, dims, str, box)) return rc;
+        if (!b_mn_major) { dims[0] = K; dims[1] = N; str[1] = ldb; box[0] = 64; box[1] = bn; }
+        else             { dims[0] = N; dims[1] = K; str[1] = ldb; box[0] = 64; box[1] = 64; }
+        if (int rc = make_tmap_bf16(&tmB, B, 2, dims, str, box)) return rc;
+    }
+    GemmParams p{};
+    p.M = M; p.N = N; p.K = K;
+    p.m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    p.n_tiles = (N + bn - 1) / bn;
+    p.k_iters_total = (K + BLOCK_K - 1) / BLOCK_K;
+    fill_epilogue(p, epi);
+    p.k_splits = (p.out_mode == 2) ? choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits) : 1;
+    finish_splits(p);
+    p.H = p.W = 1;
+    if (!a_mn_major && !b_mn_major) return dispatch_bn<OP_K2D, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
+    if (!a_mn_major && b_mn_major) return dispatch_bn<OP_K2D, OP_MN2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
+    if (a_mn_major && b_mn_major) return dispatch_bn<OP_MN2D, OP_MN2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
+    pdnn_set_error("gemm: A MN-major with B K-major is not instantiated");
+    return -2;
+}
+
+// Pixel box for a tile of `pixels` consecutive NHWC pixels (box_w == W).
+static int pixel_box(int H, int W, int batch, int pixels, int* box_h, int* box_n) {
+    const int hw = H * W;
+    if (W > pixels || (pixels % W) != 0) return -1;
+    if (hw >= pixels) {
+        if (hw % pixels != 0) return -1;
+        *box_h = pixels / W;
+        *box_n = 1;
+    } else {
+        if (pixels % hw != 0) return -1;
+        *box_h = H;
+        *box_n = pixels / hw;
+        if (batch % *box_n != 0) return -1;
+    }
+    return 0;
+}
+
+// y[n,h,w,:] = sum_{r,s,c} x[n,h+r-pad,w+s-pad,c] * wgt[k,r,s,c]   (stride 1, "same" size output)
+extern "C" int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                    int R, int S, int pad, const pdnn_epilogue_t* epi, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(C % 64 == 0, "conv_fprop: C=%d must be a multiple of 64 (use the im2col path)", C);
+    PDNN_REQUIRE(2 * pad == R - 1 && 2 * pad == S - 1, "conv_fprop: only 'same' stride-1 geometry (R=%d S=%d pad=%d)", R, S, pad);
+    GemmParams p{};
+    PDNN_REQUIRE(pixel_box(H, W, batch, BLOCK_M, &p.box_h, &p.box_n) == 0,
+                 "conv_fprop: %dx%d images (batch %d) do not tile into 128-pixel boxes", H, W, batch);
+    const long long Mll = (long long)batch * H * W;
+    PDNN_REQUIRE(Mll % BLOCK_M == 0 && Mll < (1ll << 31), "conv_fprop: pixel count must be a multiple of 128");
+    const int bn = pick_bn(Kout);
+    CUtensorMap tmA, tmB;
+    {
+        long long dims[4] = {C, W, H, batch};
+        long long str[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int box[4] = {64, W, p.box_h, p.box_n};
+        if (int rc = make_tmap_bf16(&tmA, x, 4, dims, str, box)) return rc;
+        long long wd[2] = {(long long)R * S * C, Kout};
+        long long ws[2] = {1, (long long)R * S * C};
+        int wb[2] = {64, bn};
+        if (int rc = make_tmap_bf16(&tmB, wgt, 2, wd, ws, wb)) return rc;
+    }
+    p.M = (int)Mll; p.N = Kout; p.K = R * S * C;
+    p.m_tiles = p.M / BLOCK_M;
+    p.n_tiles = (Kout + bn - 1) / bn;
+    p.k_iters_total = R * S * (C / 64);
+    p.k_splits = 1;
+    finish_splits(p);
+    p.H = H; p.W = W; p.C = C; p.R = R; p.S = S; p.pad = pad;
+    p.cblks = C / 64;
+    fill_epilogue(p, epi);
+    PDNN_REQUIRE(p.out_mode != 2 || true, "unreachable");
+    return dispatch_bn<OP_CONVK, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
+}
+
+// dW[k,r,s,c] (+)= sum_{n,h,w} dy[n,h,w,k] * x[n,h+r-pad,w+s-pad,c]; fp32 red.add into dw (KRSC).
+extern "C" int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout,
+                                    int R, int S, int pad, const pdnn_epilogue_t* epi, int k_splits,
+                                    void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(C % 64 == 0, "conv_wgrad: C=%d must be a multiple of 64", C);
+    PDNN_REQUIRE(Kout % 8 == 0, "conv_wgrad: Kout=%d must be a multiple of 8", Kout);
+    PDNN_REQUIRE(epi->out_mode == 2, "conv_wgrad accumulates with fp32 red.add (out_mode must be 2)");
+    GemmParams p{};
+    PDNN_REQUIRE(pixel_box(H, W, batch, BLOCK_K, &p.box_h, &p.box_n) == 0,
+                 "conv_wgrad: %dx%d images (batch %d) do not tile into 64-pixel boxes", H, W, batch);
+    const long long pix = (long long)batch * H * W;
+    PDNN_REQUIRE(pix % BLOCK_K == 0 && pix < (1ll << 31), "conv_wgrad: pixel count must be a multiple of 64");
+    const int bn = (C % 256 == 0) ? 256 : (C % 128 == 0 ? 128 : 64);
+    CUtensorMap tmA, tmB;
+    {
+        long long ad[2] = {Kout, pix};
+        long long as[2] = {1, Kout};
+        int ab[2] = {64, 64};
+        if (int rc = make_tmap_bf16(&tmA, dy, 2, ad, as, ab)) return rc;
+        long long dims[4] = {C, W, H, batch};
+        long long str[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int box[4] = {64, W, p.box_h, p.box_n};
+        if (int rc = make_tmap_bf16(&tmB, x, 4, dims, str, box)) return rc;
+    }
+    p.M = Kout; p.N = R * S * C; p.K = (int)pix;
+    p.m_tiles = (Kout + BLOCK_M - 1) / BLOCK_M;
+    p.cblks = C / bn;
+    p.n_tiles = R * S * p.cblks;
+    p.k_iters_total = (int)(pix / BLOCK_K);
+    p.H = H; p.W = W; p.C = C; p.R = R; p.S = S; p.pad = pad;
+    fill_epilogue(p, epi);
+    p.k_splits = choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits);
+    finish_splits(p);
+    return dispatch_bn<OP_MN2D, OP_CONVMN>(bn, tmA, tmB, p, epi->max_ctas, stream);
+}

@@ -1,0 +1,821 @@
+// Memory-bound layer kernels for sm_100a: casts/layout, im2col, BatchNorm, ReLU, pooling,
+// softmax-cross-entropy, top-k, momentum SGD, sigmoid family and a generic SIMT fp32 GEMM.
+// Activations are NHWC; `T` is __nv_bfloat16 on the tensor-core path and float on the small-shape
+// (LeNet / FC-MLP) path. All kernels use 16-byte accesses where the layout allows it and grid-stride
+// loops sized to the 148 SMs.
+#include "common.cuh"
+#include "../include/pdnn_b200.h"
+
+namespace pdnn {
+
+static inline int grid_for(long long work_items, int threads, int max_blocks = 148 * 8) {
+    long long b = (work_items + threads - 1) / threads;
+    if (b < 1) b = 1;
+    if (b > max_blocks) b = max_blocks;
+    return (int)b;
+}
+
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16(v); }
+
+// 8 consecutive bf16 <-> 8 floats
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+    u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+
+// ------------------------------------------------------------------------------------------------
+// casts and layout
+// ------------------------------------------------------------------------------------------------
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ s, __nv_bfloat16* __restrict__ d, long long n) {
+    long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    const long long stride = (long long)gridDim.x * blockDim.x * 8;
+    for (; i + 8 <= n; i += stride) {
+        float4 a = *reinterpret_cast<const float4*>(s + i);
+        float4 b = *reinterpret_cast<const float4*>(s + i + 4);
+        uint4 u;
+        u.x = pack_bf16x2(a.x, a.y); u.y = pack_bf16x2(a.z, a.w);
+        u.z = pack_bf16x2(b.x, b.y); u.w = pack_bf16x2(b.z, b.w);
+        *reinterpret_cast<uint4*>(d + i) = u;
+    }
+    if (i < n) for (long long j = i; j < n && j < i + 8; ++j) d[j] = __float2bfloat16(s[j]);
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ s, float* __restrict__ d, long long n) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) d[i] = __bfloat162float(s[i]);
+}
+
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C, int H, int W, int Cpad) {
+    const long long total = (long long)N * H * W * Cpad;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % Cpad);
+        const long long pix = i / Cpad;
+        const int w = (int)(pix % W);
+        const int h = (int)((pix / W) % H);
+        const int n = (int)(pix / ((long long)W * H));
+        float v = 0.f;
+        if (c < C) v = x[(((long long)n * C + c) * H + h) * W + w];
+        y[i] = from_f<T>(v);
+    }
+}
+
+// wt[c][R-1-r][S-1-s][k] = w[k][r][s][c]
+__global__ void wgt_flip_transpose_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt, int K, int R, int S, int C) {
+    const long long total = (long long)K * R * S * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        // i indexes the destination so that writes are coalesced
+        const int k = (int)(i % K);
+        const int s2 = (int)((i / K) % S);
+        const int r2 = (int)((i / ((long long)K * S)) % R);
+        const int c = (int)(i / ((long long)K * S * R));
+        wt[i] = w[(((long long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c];
+    }
+}
+
+__global__ void oihw_krsc_kernel(const float* __restrict__ src, float* __restrict__ dst, int K, int C, int R, int S, int to_krsc) {
+    const long long total = (long long)K * C * R * S;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        // i indexes KRSC
+        const int c = (int)(i % C);
+        const int s = (int)((i / C) % S);
+        const int r = (int)((i / ((long long)C * S)) % R);
+        const int k = (int)(i / ((long long)C * S * R));
+        const long long j = (((long long)k * C + c) * R + r) * S + s;   // OIHW
+        if (to_krsc) dst[i] = src[j]; else dst[j] = src[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// im2col / col2im (lowered convolutions)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int N, int H, int W, int C, int R, int S,
+                              int stride, int pad, int OH, int OW, int Kpad) {
+    const long long total = (long long)N * OH * OW * Kpad;
+    const int K = R * S * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i % Kpad);
+        const long long m = i / Kpad;
+        T v = from_f<T>(0.f);
+        if (k < K) {
+            const int c = k % C;
+            const int rs = k / C;
+            const int s = rs % S, r = rs / S;
+            const int ow = (int)(m % OW);
+            const int oh = (int)((m / OW) % OH);
+            const int n = (int)(m / ((long long)OW * OH));
+            const int h = oh * stride - pad + r, w = ow * stride - pad + s;
+            if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((long long)n * H + h) * W + w) * C + c];
+        }
+        col[i] = v;
+    }
+}
+// vectorised variant: C % 8 == 0, Kpad == R*S*C, bf16
+__global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int H, int W,
+                                   int C, int R, int S, int stride, int pad, int OH, int OW) {
+    const int C8 = C / 8;
+    const long long total = (long long)N * OH * OW * R * S * C8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % C8);
+        long long t = i / C8;
+        const int rs = (int)(t % (R * S));
+        const long long m = t / (R * S);
+        const int s = rs % S, r = rs / S;
+        const int ow = (int)(m % OW);
+        const int oh = (int)((m / OW) % OH);
+        const int n = (int)(m / ((long long)OW * OH));
+        const int h = oh * stride - pad + r, w = ow * stride - pad + s;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (h >= 0 && h < H && w >= 0 && w < W)
+            v = *reinterpret_cast<const uint4*>(x + (((long long)n * H + h) * W + w) * C + c8 * 8);
+        *reinterpret_cast<uint4*>(col + (m * (R * S) + rs) * C + c8 * 8) = v;
+    }
+}
+
+template <typename T>
+__global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, int N, int H, int W, int C, int R, int S,
+                              int stride, int pad, int OH, int OW, int Kpad) {
+    const long long total = (long long)N * H * W * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long long pix = i / C;
+        const int w = (int)(pix % W);
+        const int h = (int)((pix / W) % H);
+        const int n = (int)(pix / ((long long)W * H));
+        float acc = 0.f;
+        for (int r = 0; r < R; ++r) {
+            const int hh = h + pad - r;
+            if (hh < 0 || hh % stride != 0) continue;
+            const int oh = hh / stride;
+            if (oh >= OH) continue;
+            for (int s = 0; s < S; ++s) {
+                const int ww = w + pad - s;
+                if (ww < 0 || ww % stride != 0) continue;
+                const int ow = ww / stride;
+                if (ow >= OW) continue;
+                acc += to_f<T>(dcol[(((long long)n * OH + oh) * OW + ow) * Kpad + (r * S + s) * C + c]);
+            }
+        }
+        dx[i] = from_f<T>(acc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// BatchNorm (training statistics), NHWC bf16, C % 8 == 0
+// ------------------------------------------------------------------------------------------------
+// Pass 1: per-channel sum and sum of squares. Each thread owns 8 channels of a strided set of rows,
+// the block folds its row groups through shared memory, one atomicAdd per channel per block.
+template <int MODE>   // 0: stats of x ; 1: backward sums (dz, dz*xhat)
+__global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                                                        const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
+                                                        float* __restrict__ out, long long M, int C, int relu) {
+    extern __shared__ float sh[];   // [2][rows_per_iter][C]
+    const int tpr = C / 8;                        // threads per row (<= 256)
+    const int rpi = max(1, (int)blockDim.x / tpr); // rows per iteration
+    const int tid = threadIdx.x;
+    const int ct = tid % tpr;
+    const int rgrp = tid / tpr;
+    if (rgrp < rpi) {
+        float a0[8], a1[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
+        float mean[8], inv[8];
+        if (MODE == 1) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { mean[j] = mean_invstd[ct * 8 + j]; inv[j] = mean_invstd[C + ct * 8 + j]; }
+        }
+        for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += (long long)gridDim.x * rpi) {
+            const long long off = row * C + ct * 8;
+            float xv[8];
+            load8(x + off, xv);
+            if (MODE == 0) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
+            } else {
+                float dv[8];
+                load8(dy + off, dv);
+                if (relu) {
+                    float yv[8];
+                    load8(y + off, yv);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a0[j] += dv[j]; a1[j] += dv[j] * (xv[j] - mean[j]) * inv[j]; }
+            }
+        }
+        float* s0 = sh + (long long)rgrp * C + ct * 8;
+        float* s1 = sh + (long long)rpi * C + (long long)rgrp * C + ct * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0[j] = a0[j]; s1[j] = a1[j]; }
+    }
+    __syncthreads();
+    for (int c = tid; c < C; c += blockDim.x) {
+        float t0 = 0.f, t1 = 0.f;
+        for (int g = 0; g < rpi; ++g) { t0 += sh[(long long)g * C + c]; t1 += sh[(long long)rpi * C + (long long)g * C + c]; }
+        atomicAdd(out + c, t0);
+        atomicAdd(out + C + c, t1);
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
+                                                           float* __restrict__ mean_invstd, float* running_mean, float* running_var,
+                                                           long long M, int C, float eps, float momentum, int relu) {
+    const int tpr = C / 8;
+    const float invM = 1.f / (float)M;
+    const long long total = M * tpr;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int ct = (int)(i % tpr);
+        const long long row = i / tpr;
+        float sc[8], sf[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = ct * 8 + j;
+            const float mean = stats[c] * invM;
+            const float var = fmaxf(stats[C + c] * invM - mean * mean, 0.f);
+            const float inv = rsqrtf(var + eps);
+            sc[j] = gamma[c] * inv;
+            sf[j] = beta[c] - mean * sc[j];
+            if (row == 0) {
+                mean_invstd[c] = mean;
+                mean_invstd[C + c] = inv;
+                if (running_mean != nullptr) {
+                    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                    const float unbiased = M > 1 ? var * (float)M / (float)(M - 1) : var;
+                    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+                }
+            }
+        }
+        const long long off = row * C + ct * 8;
+        float v[8];
+        load8(x + off, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = v[j] * sc[j] + sf[j];
+        if (residual != nullptr) {
+            float r[8];
+            load8(residual + off, r);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += r[j];
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        store8(y + off, v);
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
+                                                           const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ sums,
+                                                           __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu) {
+    const int tpr = C / 8;
+    const float invM = 1.f / (float)M;
+    const long long total = M * tpr;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int ct = (int)(i % tpr);
+        const long long row = i / tpr;
+        const long long off = row * C + ct * 8;
+        float xv[8], dv[8];
+        load8(x + off, xv);
+        load8(dy + off, dv);
+        if (relu) {
+            float yv[8];
+            load8(y + off, yv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+        }
+        if (dres != nullptr) store8(dres + off, dv);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = ct * 8 + j;
+            const float mean = mean_invstd[c], inv = mean_invstd[C + c];
+            const float s0 = sums[c], s1 = sums[C + c];
+            const float xhat = (xv[j] - mean) * inv;
+            o[j] = gamma[c] * inv * (dv[j] - s0 * invM - xhat * s1 * invM);
+            if (row == 0) { dgamma[c] = s1; dbeta[c] = s0; }
+        }
+        store8(dx + off, o);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ReLU / add / pooling
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void relu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        y[i] = from_f<T>(fmaxf(to_f<T>(x[i]), 0.f));
+}
+template <typename T>
+__global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        dx[i] = to_f<T>(y[i]) > 0.f ? dy[i] : from_f<T>(0.f);
+}
+__global__ void relu_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        float v[8];
+        load8(x + i * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        store8(y + i * 8, v);
+    }
+}
+__global__ void relu_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, long long n8) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        float yv[8], dv[8];
+        load8(y + i * 8, yv);
+        load8(dy + i * 8, dv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+        store8(dx + i * 8, dv);
+    }
+}
+__global__ void add_vec8_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ o, long long n8, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        float av[8], bv[8];
+        load8(a + i * 8, av);
+        load8(b + i * 8, bv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) av[j] += bv[j];
+        store8(o + i * 8, av);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (long long j = n8 * 8; j < n; ++j) o[j] = __float2bfloat16(__bfloat162float(a[j]) + __bfloat162float(b[j]));
+}
+
+template <typename T>
+__global__ void maxpool2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C) {
+    const int OH = H / 2, OW = W / 2;
+    const long long total = (long long)N * OH * OW * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long long p = i / C;
+        const int ow = (int)(p % OW), oh = (int)((p / OW) % OH), n = (int)(p / ((long long)OW * OH));
+        const T* b = x + (((long long)n * H + oh * 2) * W + ow * 2) * C + c;
+        float m = fmaxf(fmaxf(to_f<T>(b[0]), to_f<T>(b[C])), fmaxf(to_f<T>(b[(long long)W * C]), to_f<T>(b[(long long)W * C + C])));
+        y[i] = from_f<T>(m);
+    }
+}
+// gradient goes to the first max of each window (torch semantics)
+template <typename T>
+__global__ void maxpool2_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, int N, int H, int W, int C) {
+    const int OH = H / 2, OW = W / 2;
+    const long long total = (long long)N * OH * OW * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long long p = i / C;
+        const int ow = (int)(p % OW), oh = (int)((p / OW) % OH), n = (int)(p / ((long long)OW * OH));
+        const long long base = (((long long)n * H + oh * 2) * W + ow * 2) * C + c;
+        const long long offs[4] = {0, C, (long long)W * C, (long long)W * C + C};
+        const float m = to_f<T>(y[i]);
+        bool given = false;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const bool hit = !given && to_f<T>(x[base + offs[q]]) == m;
+            dx[base + offs[q]] = hit ? dy[i] : from_f<T>(0.f);
+            given = given || hit;
+        }
+    }
+}
+__global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+    const long long total = (long long)N * C;
+    const float inv = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long long n = i / C;
+        float acc = 0.f;
+        for (int p = 0; p < HW; ++p) acc += __bfloat162float(x[(n * HW + p) * C + c]);
+        y[i] = __float2bfloat16(acc * inv);
+    }
+}
+__global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+    const long long total = (long long)N * HW * C;
+    const float inv = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        const long long n = i / ((long long)HW * C);
+        dx[i] = __float2bfloat16(__bfloat162float(dy[n * C + c]) * inv);
+    }
+}
+
+// column sums over rows (bias gradients). One block per 32-column strip, warps stride over rows.
+template <typename T>
+__global__ void __launch_bounds__(256) col_sum_kernel(const T* __restrict__ dy, long long ld, float* __restrict__ out, long long M, int C, int accumulate) {
+    __shared__ float sh[8][33];
+    const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int w = threadIdx.x >> 5;
+    float acc = 0.f;
+    if (c < C)
+        for (long long r = (long long)blockIdx.y * 8 + w; r < M; r += (long long)gridDim.y * 8) acc += to_f<T>(dy[r * ld + c]);
+    sh[w][threadIdx.x & 31] = acc;
+    __syncthreads();
+    if (w == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) t += sh[g][threadIdx.x];
+        if (gridDim.y == 1 && !accumulate) out[c] = t; else atomicAdd(out + c, t);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// softmax cross-entropy (mean) forward + backward, one warp per row
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) cross_entropy_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
+                                                            float* __restrict__ loss, T* __restrict__ dlogits, int* __restrict__ correct,
+                                                            int B, int classes, int ld) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    const float invB = 1.f / (float)B;
+    float loss_acc = 0.f;
+    int hit_acc = 0;
+    for (int row = warp; row < B; row += nwarps) {
+        const T* lp = logits + (long long)row * ld;
+        const int label = (int)labels[row];
+        float mx = -INFINITY;
+        int arg = 0x7fffffff;
+        for (int c = lane; c < classes; c += 32) {
+            const float v = to_f<T>(lp[c]);
+            if (v > mx) { mx = v; arg = c; }
+        }
+        // warp argmax (lowest index wins ties)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+            const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+            if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+        }
+        float se = 0.f;
+        for (int c = lane; c < classes; c += 32) se += __expf(to_f<T>(lp[c]) - mx);
+        se = warp_sum(se);
+        const float lse = mx + __logf(se);
+        if (dlogits != nullptr) {
+            T* dp = dlogits + (long long)row * ld;
+            for (int c = lane; c < ld; c += 32) {
+                float g = 0.f;
+                if (c < classes) g = (__expf(to_f<T>(lp[c]) - lse) - (c == label ? 1.f : 0.f)) * invB;
+                dp[c] = from_f<T>(g);
+            }
+        }
+        if (lane == 0) {
+            loss_acc += (lse - to_f<T>(lp[label])) * invB;
+            hit_acc += (arg == label);
+        }
+    }
+    if (lane == 0) {
+        if (loss != nullptr) atomicAdd(loss, loss_acc);
+        if (correct != nullptr && hit_acc) atomicAdd(correct, hit_acc);
+    }
+}
+
+__global__ void topk_correct_kernel(const float* __restrict__ logits, const long long* __restrict__ labels, int B, int classes, int ld,
+                                    int k0, int k1, int k2, int k3, int nk, int* __restrict__ correct) {
+    for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < B; row += gridDim.x * blockDim.x) {
+        const float* lp = logits + (long long)row * ld;
+        const int label = (int)labels[row];
+        const float lv = lp[label];
+        int rank = 0;   // number of classes strictly better (or equal with a lower index)
+        for (int c = 0; c < classes; ++c) {
+            const float v = lp[c];
+            rank += (v > lv) || (v == lv && c < label);
+        }
+        const int ks[4] = {k0, k1, k2, k3};
+        for (int i = 0; i < nk; ++i) if (rank < ks[i]) atomicAdd(correct + i, 1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// momentum SGD on flat buffers
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sgd_momentum_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
+                                                           __nv_bfloat16* __restrict__ wb, long long n, float lr, float mu, float scale, int first) {
+    const long long n4 = n / 4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        float4 gv = reinterpret_cast<const float4*>(g)[i];
+        float4 wv = reinterpret_cast<float4*>(w)[i];
+        float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m != nullptr && !first) mv = reinterpret_cast<float4*>(m)[i];
+        mv.x = mu * mv.x + scale * gv.x; mv.y = mu * mv.y + scale * gv.y;
+        mv.z = mu * mv.z + scale * gv.z; mv.w = mu * mv.w + scale * gv.w;
+        wv.x -= lr * mv.x; wv.y -= lr * mv.y; wv.z -= lr * mv.z; wv.w -= lr * mv.w;
+        if (m != nullptr) reinterpret_cast<float4*>(m)[i] = mv;
+        reinterpret_cast<float4*>(w)[i] = wv;
+        if (wb != nullptr) {
+            uint2 u;
+            u.x = pack_bf16x2(wv.x, wv.y); u.y = pack_bf16x2(wv.z, wv.w);
+            reinterpret_cast<uint2*>(wb)[i] = u;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (long long j = n4 * 4; j < n; ++j) {
+            float mv = (m != nullptr && !first) ? m[j] : 0.f;
+            mv = mu * mv + scale * g[j];
+            w[j] -= lr * mv;
+            if (m != nullptr) m[j] = mv;
+            if (wb != nullptr) wb[j] = __float2bfloat16(w[j]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// sigmoid family
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void sigmoid_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        y[i] = from_f<T>(1.f / (1.f + __expf(-to_f<T>(x[i]))));
+}
+template <typename T>
+__global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float s = to_f<T>(y[i]);
+        dx[i] = from_f<T>(to_f<T>(dy[i]) * s * (1.f - s));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// generic SIMT fp32 GEMM: 64x64 tile, 16-deep k step, 256 threads, 4x4 micro tile
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gemm_simt_kernel(const float* __restrict__ A, long long sam, long long sak,
+                                                        const float* __restrict__ B, long long sbk, long long sbn,
+                                                        float* __restrict__ C, long long ldc, int M, int N, int K, float alpha,
+                                                        const float* __restrict__ bias, int relu, int accumulate) {
+    __shared__ float As[16][64 + 4];
+    __shared__ float Bs[16][64 + 4];
+    const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    float acc[4][4] = {};
+    for (int k0 = 0; k0 < K; k0 += 16) {
+        for (int i = threadIdx.x; i < 64 * 16; i += 256) {
+            const int kk = i % 16, mm = i / 16;
+            const int gm = m0 + mm, gk = k0 + kk;
+            As[kk][mm] = (gm < M && gk < K) ? A[gm * sam + gk * sak] : 0.f;
+            const int gn = n0 + mm;
+            Bs[kk][mm] = (gn < N && gk < K) ? B[gk * sbk + gn * sbn] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            float a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = As[kk][ty * 4 + i]; b[i] = Bs[kk][tx * 4 + i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * b[j];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gm = m0 + ty * 4 + i;
+        if (gm >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int gn = n0 + tx * 4 + j;
+            if (gn >= N) continue;
+            float v = alpha * acc[i][j];
+            if (bias != nullptr) v += bias[gn];
+            if (accumulate) v += C[gm * ldc + gn];
+            if (relu) v = fmaxf(v, 0.f);
+            C[gm * ldc + gn] = v;
+        }
+    }
+}
+
+}  // namespace pdnn
+
+using namespace pdnn;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+#define BF(p) reinterpret_cast<__nv_bfloat16*>(p)
+#define CBF(p) reinterpret_cast<const __nv_bfloat16*>(p)
+#define LAUNCH_OK()                        \
+    do {                                   \
+        PDNN_COUNT_LAUNCH();               \
+        PDNN_CUDA_CHECK(cudaGetLastError()); \
+        return 0;                          \
+    } while (0)
+
+extern "C" int pdnn_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
+    if (n <= 0) return 0;
+    cast_f32_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST(stream)>>>(src, BF(dst), n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream) {
+    if (n <= 0) return 0;
+    cast_bf16_f32_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(src), dst, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, void* stream) {
+    nchw_to_nhwc_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * Cpad, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, H, W, Cpad);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_nchw_f32_to_nhwc_f32(const float* x, float* y, int N, int C, int H, int W, int Cpad, void* stream) {
+    nchw_to_nhwc_kernel<float><<<grid_for((long long)N * H * W * Cpad, 256), 256, 0, ST(stream)>>>(x, y, N, C, H, W, Cpad);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_wgt_flip_transpose(const void* w, void* wt, int K, int R, int S, int C, void* stream) {
+    wgt_flip_transpose_kernel<<<grid_for((long long)K * R * S * C, 256), 256, 0, ST(stream)>>>(CBF(w), BF(wt), K, R, S, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_oihw_to_krsc_f32(const float* src, float* dst, int K, int C, int R, int S, int to_krsc, void* stream) {
+    oihw_krsc_kernel<<<grid_for((long long)K * R * S * C, 256), 256, 0, ST(stream)>>>(src, dst, K, C, R, S, to_krsc);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_im2col_bf16(const void* x, void* col, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
+                                int OW, int Kpad, void* stream) {
+    if (C % 8 == 0 && Kpad == R * S * C) {
+        const long long total = (long long)N * OH * OW * R * S * (C / 8);
+        im2col_vec8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW);
+    } else {
+        const long long total = (long long)N * OH * OW * Kpad;
+        im2col_kernel<__nv_bfloat16><<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    }
+    LAUNCH_OK();
+}
+extern "C" int pdnn_im2col_f32(const float* x, float* col, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
+                               int OW, int Kpad, void* stream) {
+    const long long total = (long long)N * OH * OW * Kpad;
+    im2col_kernel<float><<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(x, col, N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_col2im_bf16(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
+                                int OW, int Kpad, void* stream) {
+    col2im_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * C, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_col2im_f32(const float* dcol, float* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
+                               int OW, int Kpad, void* stream) {
+    col2im_kernel<float><<<grid_for((long long)N * H * W * C, 256, 148 * 16), 256, 0, ST(stream)>>>(dcol, dx, N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    LAUNCH_OK();
+}
+
+static int bn_reduce_cfg(int C, int* rpi, size_t* smem) {
+    const int tpr = C / 8;
+    *rpi = tpr >= 256 ? 1 : 256 / tpr;
+    *smem = (size_t)2 * (*rpi) * C * sizeof(float);
+    return 0;
+}
+extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C, void* stream) {
+    PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
+    int rpi; size_t smem;
+    bn_reduce_cfg(C, &rpi, &smem);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
+                                 void* y, float* mean_invstd, float* running_mean, float* running_var, long long M, int C,
+                                 float eps, float momentum, int relu, void* stream) {
+    PDNN_REQUIRE(C % 8 == 0, "bn: C=%d must be a multiple of 8", C);
+    bn_fwd_apply_kernel<<<grid_for(M * (C / 8), 256, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
+                                                                                     running_mean, running_var, M, C, eps, momentum, relu);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums, long long M,
+                                  int C, int relu, void* stream) {
+    PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
+    int rpi; size_t smem;
+    bn_reduce_cfg(C, &rpi, &smem);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,
+                                 const float* sums, void* dx, void* dresidual, float* dgamma, float* dbeta, long long M, int C,
+                                 int relu, void* stream) {
+    bn_bwd_apply_kernel<<<grid_for(M * (C / 8), 256, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
+                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream) {
+    if (n % 8 == 0) relu_fwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n / 8);
+    else relu_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
+    if (n % 8 == 0) relu_bwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n / 8);
+    else relu_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_relu_fwd_f32(const float* x, float* y, long long n, void* stream) {
+    relu_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_relu_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream) {
+    relu_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_add_bf16(const void* a, const void* b, void* out, long long n, void* stream) {
+    add_vec8_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, ST(stream)>>>(CBF(a), CBF(b), BF(out), n / 8, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_maxpool2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
+    maxpool2_fwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, H, W, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_maxpool2_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, void* stream) {
+    maxpool2_bwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), BF(dx), N, H, W, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_maxpool2_fwd_f32(const float* x, float* y, int N, int H, int W, int C, void* stream) {
+    maxpool2_fwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, N, H, W, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_maxpool2_bwd_f32(const float* x, const float* y, const float* dy, float* dx, int N, int H, int W, int C, void* stream) {
+    maxpool2_bwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, dy, dx, N, H, W, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+    avgpool_fwd_kernel<<<grid_for((long long)N * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+    avgpool_bwd_kernel<<<grid_for((long long)N * HW * C, 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_col_sum(const void* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream) {
+    int gy = (int)((M + 255) / 256);
+    if (gy > 64) gy = 64;
+    if (gy < 1) gy = 1;
+    if (gy > 1 && !accumulate) PDNN_CUDA_CHECK(cudaMemsetAsync(out, 0, sizeof(float) * C, ST(stream)));
+    col_sum_kernel<__nv_bfloat16><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(CBF(dy), ld, out, M, C, accumulate);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_col_sum_f32(const float* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream) {
+    int gy = (int)((M + 255) / 256);
+    if (gy > 64) gy = 64;
+    if (gy < 1) gy = 1;
+    if (gy > 1 && !accumulate) PDNN_CUDA_CHECK(cudaMemsetAsync(out, 0, sizeof(float) * C, ST(stream)));
+    col_sum_kernel<float><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(dy, ld, out, M, C, accumulate);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_cross_entropy_fwd_bwd(const void* logits, const long long* labels, float* loss, void* dlogits, int* correct,
+                                          int B, int classes, int ld, void* stream) {
+    cross_entropy_kernel<__nv_bfloat16><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(CBF(logits), labels, loss, BF(dlogits), correct, B, classes, ld);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_cross_entropy_fwd_bwd_f32(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
+                                              int B, int classes, int ld, void* stream) {
+    cross_entropy_kernel<float><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(logits, labels, loss, dlogits, correct, B, classes, ld);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_topk_correct(const float* logits, const long long* labels, int B, int classes, int ld, const int* ks_host, int nk,
+                                 int* correct, void* stream) {
+    PDNN_REQUIRE(nk >= 1 && nk <= 4, "topk: 1..4 k values supported");
+    int ks[4] = {0, 0, 0, 0};
+    for (int i = 0; i < nk; ++i) ks[i] = ks_host[i];
+    topk_correct_kernel<<<grid_for(B, 128), 128, 0, ST(stream)>>>(logits, labels, B, classes, ld, ks[0], ks[1], ks[2], ks[3], nk, correct);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_sgd_momentum(float* w, const float* g, float* m, void* w_bf16, long long n, float lr, float mu, float scale,
+                                 int first_step, void* stream) {
+    if (n <= 0) return 0;
+    sgd_momentum_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, ST(stream)>>>(w, g, m, BF(w_bf16), n, lr, mu, scale, first_step);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_sigmoid_fwd(const void* x, void* y, long long n, void* stream) {
+    sigmoid_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_sigmoid_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
+    sigmoid_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_sigmoid_fwd_f32(const float* x, float* y, long long n, void* stream) {
+    sigmoid_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_sigmoid_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream) {
+    sigmoid_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, const float* B, int transB, long long ldb, float* C,
+                                  long long ldc, int M, int N, int K, float alpha, const float* bias, int relu, int accumulate,
+                                  void* stream) {
+    // op(A)[m][k]: transA ? A[k*lda+m] : A[m*lda+k];  op(B)[k][n]: transB ? B[n*ldb+k] : B[k*ldb+n]
+    const long long sam = transA ? 1 : lda, sak = transA ? lda : 1;
+    const long long sbk = transB ? 1 : ldb, sbn = transB ? ldb : 1;
+    dim3 grid((N + 63) / 64, (M + 63) / 64);
+    gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate);
+    LAUNCH_OK();
+}

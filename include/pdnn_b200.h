@@ -1,0 +1,203 @@
+/* C ABI of libpdnn_b200.so — the sm_100a kernel library of pytorch_distributed_nn_b200.
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure it returns non-zero and pdnn_last_error()
+ *     gives the message (thread-local).
+ *   - pointers are device pointers unless the comment says otherwise; `stream` is a cudaStream_t.
+ *   - activations are NHWC bf16, parameters / gradients / optimizer state are fp32 unless stated.
+ *   - "ref:" comments cite the component of chao1224/pytorch_distributed_nn each entry point covers
+ *     (paths relative to the reference root).
+ */
+#ifndef PDNN_B200_H
+#define PDNN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* pdnn_last_error(void);
+int pdnn_version(void);
+/* Number of kernel launches issued through this library by the calling process (all threads). */
+long long pdnn_launch_count(void);
+void pdnn_reset_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * GEMM / convolution on tcgen05 + TMEM + TMA (csrc/gemm_tcgen05.cu)
+ * ------------------------------------------------------------------------------------------- */
+typedef struct pdnn_epilogue {
+    void* out;                 /* [M][ldo] */
+    long long ldo;             /* row stride in elements */
+    int out_mode;              /* 0 = bf16 store, 1 = fp32 store, 2 = fp32 red.add (caller zero-fills) */
+    int relu;                  /* clamp at 0 after bias/residual */
+    float alpha;               /* scale applied to the accumulator */
+    const float* bias;         /* [N] or NULL */
+    const void* residual;      /* bf16 [M][ldo] or NULL (bf16 out only) */
+    const uint32_t* guard_closed; /* straggler abort guard (both NULL = disabled): the kernel returns */
+    const uint32_t* guard_step;   /*   at once when *guard_closed >= *guard_step                      */
+    int max_ctas;              /* 0 = one CTA per SM */
+} pdnn_epilogue_t;
+
+/* D[M][N] = alpha * A * B (+bias)(+residual)(relu). A is [M][K] (a_mn_major=0, K contiguous, row
+ * stride lda) or stored as [K][M] (a_mn_major=1). B is [N][K] (b_mn_major=0) or stored as [K][N]
+ * (b_mn_major=1). bf16 inputs, fp32 accumulation in TMEM. K-strides must be multiples of 8 elements.
+ * ref: nn.Linear fwd/bwd (pytorch_code/model_ops/lenet.py:45-46, resnet.py:78), cblas_dgemm NN/NT/TN
+ * (MPI_code/src/util/util.h:35-81), numpy dot (pure_py_code/nn/nn_layer.py:79-92). */
+int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, int b_mn_major,
+                   long long ldb, int M, int N, int K, const pdnn_epilogue_t* epi, int k_splits,
+                   void* stream);
+
+/* Stride-1 "same" convolution forward as implicit GEMM. x: NHWC bf16 [batch][H][W][C], C % 64 == 0;
+ * wgt: bf16 [Kout][R][S][C]; out rows are output pixels in NHWC order, ldo >= Kout.
+ * Data-gradient of the same conv = this entry point on dy with pdnn_wgt_flip_transpose()'d weights.
+ * ref: nn.Conv2d 3x3 fwd / bwd-data (pytorch_code/model_ops/resnet.py:19-21,72; resnet_split.py:28,34). */
+int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                         int R, int S, int pad, const pdnn_epilogue_t* epi, void* stream);
+
+/* Weight gradient of the same conv: dw[Kout][R][S][C] (fp32) += dy^T * im2col(x). out_mode must be 2.
+ * ref: nn.Conv2d bwd-filter (same call sites). */
+int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout,
+                         int R, int S, int pad, const pdnn_epilogue_t* epi, int k_splits, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Layer kernels (csrc/nn_kernels.cu)
+ * ------------------------------------------------------------------------------------------- */
+int pdnn_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+int pdnn_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream);
+/* NCHW fp32 images -> NHWC bf16 with the channel dim zero-padded to Cpad (input staging). */
+int pdnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, void* stream);
+/* KRSC bf16 -> [C][R][S][K] with (r,s) mirrored: the filter bank that turns dgrad into fprop. */
+int pdnn_wgt_flip_transpose(const void* w, void* wt, int K, int R, int S, int C, void* stream);
+/* fp32 OIHW (torch) <-> KRSC (ours). */
+int pdnn_oihw_to_krsc_f32(const float* src, float* dst, int K, int C, int R, int S, int to_krsc, void* stream);
+
+/* im2col for the lowered convs (stride 2, 1x1 shortcuts, stems, LeNet 5x5).
+ * col[(n,oh,ow)][Kpad], k = (r*S+s)*C + c, columns >= R*S*C are zero. */
+int pdnn_im2col_bf16(const void* x, void* col, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                     int OH, int OW, int Kpad, void* stream);
+/* dx[n,h,w,c] = sum over the (oh,ow,r,s) that touch it of dcol[(n,oh,ow)][(r*S+s)*C+c]  (gather form). */
+int pdnn_col2im_bf16(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                     int OH, int OW, int Kpad, void* stream);
+
+/* BatchNorm2d, training mode (batch statistics), NHWC bf16, M = N*H*W rows, C channels.
+ * ref: nn.BatchNorm2d (pytorch_code/model_ops/resnet.py:20,22,28; resnet_split.py:31,37,46,128).
+ * stats: [2][C] fp32 scratch that must be zero on entry to bn_fwd_stats (sum, sum of squares);
+ * mean_invstd: [2][C] fp32 saved for backward. running_mean/var updated in place (may be NULL). */
+int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C, void* stream);
+int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta,
+                      const void* residual, void* y, float* mean_invstd, float* running_mean,
+                      float* running_var, long long M, int C, float eps, float momentum, int relu,
+                      void* stream);
+/* sums: [2][C] fp32, zero on entry: sum(dz), sum(dz * xhat), dz = dy * (y > 0 if relu). */
+int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums,
+                       long long M, int C, int relu, void* stream);
+/* dx = gamma*invstd*(dz - sum_dz/M - xhat*sum_dzxhat/M); dresidual = dz (optional); dgamma/dbeta fp32. */
+int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd,
+                      const float* gamma, const float* sums, void* dx, void* dresidual, float* dgamma,
+                      float* dbeta, long long M, int C, int relu, void* stream);
+
+int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream);
+int pdnn_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream);
+int pdnn_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
+/* 2x2/2 max pool, NHWC bf16. ref: nn.MaxPool2d (pytorch_code/model_ops/lenet.py:48). */
+int pdnn_maxpool2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream);
+int pdnn_maxpool2_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, void* stream);
+/* Average pool over the whole HxW map. ref: F.avg_pool2d(out, 4) (pytorch_code/model_ops/resnet.py:94). */
+int pdnn_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int pdnn_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+/* dbias[c] = sum_rows dy[row][c]  (ref: distributed_worker.py:172-173, sum(dL/dlogits, axis=0)). */
+int pdnn_col_sum(const void* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream);
+
+/* Fused softmax cross-entropy, mean reduction: loss (1 fp32, zero on entry) and dlogits = (p - onehot)/B.
+ * logits bf16 [B][ld]; dlogits bf16 [B][ld] (padding columns written as 0); correct[0] += #argmax hits.
+ * ref: nn.CrossEntropyLoss (pytorch_code/distributed_worker.py:86,161; nn_ops/__init__.py:44) and
+ * accuracy() (nn_ops/__init__.py:13-26). */
+int pdnn_cross_entropy_fwd_bwd(const void* logits, const long long* labels, float* loss, void* dlogits,
+                               int* correct, int B, int classes, int ld, void* stream);
+/* prec@k counts: correct[i] = #rows whose label is within the top ks[i] logits (fp32 logits). */
+int pdnn_topk_correct(const float* logits, const long long* labels, int B, int classes, int ld, const int* ks_host,
+                      int nk, int* correct, void* stream);
+
+/* Momentum SGD on flat fp32 buffers: g' = scale*g; m = mu*m + g' (m = g' when first_step); w -= lr*m.
+ * Optionally also writes the bf16 copy of w. ref: torch.optim.SGD (nn_ops/__init__.py:43,73),
+ * update_params_dist_version (sync_replicas_master_nn.py:22-28). */
+int pdnn_sgd_momentum(float* w, const float* g, float* m, void* w_bf16, long long n, float lr, float mu,
+                      float scale, int first_step, void* stream);
+
+/* FC/sigmoid family (native counterpart of MPI_code/src/util/util.h:84-177 and pure_py_code/nn). */
+int pdnn_sigmoid_fwd(const void* x, void* y, long long n, void* stream);               /* bf16 */
+int pdnn_sigmoid_bwd(const void* y, const void* dy, void* dx, long long n, void* stream); /* dx = dy*y*(1-y) */
+
+/* Generic fp32 SIMT GEMM for shapes the tensor-core path cannot take (LeNet: N = 10/20/50, K = 25/500).
+ * C[M][N] = alpha * op(A) * op(B) (+bias)(relu), (+= C when accumulate). A/B/C row-major fp32. */
+int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, const float* B, int transB, long long ldb,
+                       float* C, long long ldc, int M, int N, int K, float alpha, const float* bias, int relu,
+                       int accumulate, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Parameter-server kernels over peer memory (csrc/ps_kernels.cu)
+ * ------------------------------------------------------------------------------------------- */
+#define PDNN_MAX_WORKERS 16
+
+/* Worker -> master gradient push (ref: communicator.Isend(grad, dest=0, tag=88+l),
+ * pytorch_code/model_ops/lenet.py:119, distributed_worker.py:175). Copies (and optionally casts
+ * fp32 -> bf16) `n` gradient elements into the master's slot for this worker (a peer pointer), then
+ * publishes `step` in the master-side arrival flag with release.sys semantics. */
+int pdnn_ps_push(const float* grad, void* slot_peer, long long n, int slot_is_bf16, uint32_t* flag_peer,
+                 uint32_t step, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
+                 void* stream);
+
+typedef struct pdnn_ps_master {
+    /* inputs */
+    const void* slots[PDNN_MAX_WORKERS];     /* per-worker gradient slot on the master (bf16 or fp32) */
+    uint32_t* arrival_flags;                 /* [n_workers] written by workers: step number */
+    void* worker_weights[PDNN_MAX_WORKERS];  /* peer pointers: each worker's weight buffer */
+    uint32_t* worker_ready[PDNN_MAX_WORKERS];/* peer pointers: weights_ready word of each worker */
+    uint32_t* worker_closed[PDNN_MAX_WORKERS];/* peer pointers: step_closed word of each worker */
+    void* multicast_weights;                 /* NVLS multicast address of the weight buffers or NULL */
+    float* master_w;                         /* fp32 master weights */
+    float* momentum;                         /* fp32 momentum buffer */
+    uint32_t* control;                       /* >= 64 words of zero-initialised master-local scratch */
+    long long n;                             /* number of parameters */
+    int n_workers;
+    int k;                                   /* aggregate the first k complete gradient sets */
+    int slot_is_bf16;
+    int weights_are_bf16;
+    int avg_mode;                            /* 0: 1/k, 1: 1/n (reference python), 2: 1/received */
+    float lr, mu;
+    uint32_t step;                           /* step being closed; workers are released with step+1 */
+    long long deadline_ns;                   /* >0: interval policy, close with whatever arrived */
+    int max_ctas;
+} pdnn_ps_master_t;
+
+/* Master: wait for the first k arrivals of `step`, publish the kill mask to the late workers
+ * (step_closed = step in their memory), sum the selected slots in rank order, apply 1/k + momentum SGD
+ * to the fp32 master copy, cast and store the new weights into every worker's buffer (unicast peer
+ * stores or one multimem store), then release the workers (weights_ready = step+1).
+ * ref: SyncReplicasMaster_NN.train hot loop, pytorch_code/sync_replicas_master_nn.py:117-228
+ * (Waitany/aggregate/kill/update/Bcast) and MPI_code/src/distributed/sync_replicas_master_nn.h:46-137.
+ * result_host_or_dev (device, 4 words): [0]=selected mask, [1]=kill mask, [2]=#received, [3]=step. */
+int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* stream);
+
+/* Worker: block the stream until *ready_flag >= step (ref: distributed_worker.py:202-208 irecv tag 10). */
+int pdnn_ps_wait_flag(const uint32_t* flag, uint32_t value, uint32_t* cur_step_word, long long timeout_ns,
+                      void* stream);
+/* Device-side straggler injection: busy-wait `ns` nanoseconds on %globaltimer (aborts early when the
+ * guard closes). ref: pure_py_code/distributed_worker.py:130-132 (time.sleep(0.5) per layer). */
+int pdnn_delay(long long ns, const uint32_t* guard_closed, const uint32_t* guard_step, void* stream);
+int pdnn_set_word(uint32_t* p, uint32_t v, void* stream);
+
+/* Peer-memory plumbing (CUDA IPC): handle is 64 bytes. */
+int pdnn_ipc_get_handle(void* dev_ptr, void* handle_out64);
+int pdnn_ipc_open_handle(const void* handle64, void** dev_ptr_out);
+int pdnn_ipc_close(void* dev_ptr);
+int pdnn_enable_peer_access(int peer_device);
+
+/* Link microbenchmarks: copy n bytes local->dst (peer) with 16-byte stores. */
+int pdnn_p2p_copy(const void* src, void* dst, long long nbytes, int max_ctas, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDNN_B200_H */
