@@ -18,6 +18,10 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
+# fp32 references must be true fp32 (no TF32 in cuDNN / cuBLAS)
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 CASES = {}
 
 
@@ -30,7 +34,7 @@ def rel_err(got, ref):
     got = got.float()
     ref = ref.float()
     denom = ref.abs().max().clamp_min(1e-6)
-    return float((got - ref).abs().max() / denom)
+    return float(((got - ref).abs().max() / denom).detach())
 
 
 def report(name, err, tol, extra=""):
