@@ -31,6 +31,8 @@ def check(name, batch):
     missing = ref.load_state_dict(sd, strict=False)
     assert not missing.missing_keys, missing
     ref.train()
+    if net.dtype == torch.bfloat16:
+        emulate_bf16_storage(ref)
     shp = input_shape(name)
     x = torch.randn(batch, *shp, device="cuda")
     if net.dtype == torch.bfloat16:
@@ -48,16 +50,19 @@ def check(name, batch):
     grads = net.export_grads()
     worst = (0.0, None)
     cos_min = 1.0
+    gmax = max(float(p.grad.norm()) for p in ref.parameters())
     for k, p in ref.named_parameters():
         g = grads[k]
         r = p.grad
+        if float(r.norm()) < 1e-5 * gmax:     # analytically-zero gradients (conv bias in front of BN): pure noise
+            continue
         err = float((g - r).abs().max() / r.abs().max().clamp_min(1e-8))
         cos = float(torch.nn.functional.cosine_similarity(g.flatten(), r.flatten(), dim=0))
         cos_min = min(cos_min, cos)
         if err > worst[0]:
             worst = (err, k)
     tol = 1e-3 if net.dtype == torch.float32 else 6e-2
-    ok = e_logits < tol and e_loss < tol and cos_min > (0.9999 if net.dtype == torch.float32 else 0.99)
+    ok = e_logits < tol and e_loss < tol and cos_min > (0.9999 if net.dtype == torch.float32 else 0.995)
     print(f"ENGINE {name} batch={batch} {'ok' if ok else 'FAIL'} logits_rel={e_logits:.3e} loss_rel={e_loss:.3e} "
           f"worst_grad_rel={worst[0]:.3e} ({worst[1]}) min_grad_cos={cos_min:.5f} loss={float(loss):.4f}", flush=True)
     return ok
@@ -112,6 +117,20 @@ def timeit(name, batch, iters=10):
     rms = s.elapsed_time(e) / iters
     print(f"STEP {name} batch={batch} ours_ms={ms:.3f} ({batch / ms * 1e3:.0f} img/s, {launches:.0f} launches, "
           f"host_issue_ms={(t1 - t0) / iters * 1e3:.3f}) torch_eager_bf16_ms={rms:.3f} ({batch / rms * 1e3:.0f} img/s)", flush=True)
+
+
+def emulate_bf16_storage(model):
+    """Make the fp32 oracle round activations to bf16 at the points where the engine stores them (conv / linear /
+    BN outputs and block outputs). Without this, ReLU masks of near-zero activations flip between the two runs and
+    the comparison measures that chaos instead of kernel correctness."""
+    from pytorch_distributed_nn_b200.models import resnet as R
+
+    def rnd(mod, inp, out):
+        return out.bfloat16().float()   # the cast's backward also rounds the gradient to bf16, as the engine does
+
+    for m in model.modules():
+        if isinstance(m, (torch.nn.Conv2d, torch.nn.Linear, torch.nn.BatchNorm2d, R.BasicBlock, R.Bottleneck)):
+            m.register_forward_hook(rnd)
 
 
 def main():

@@ -558,19 +558,24 @@ __global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict_
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const float* __restrict__ A, long long sam, long long sak,
                                                         const float* __restrict__ B, long long sbk, long long sbn,
                                                         float* __restrict__ C, long long ldc, int M, int N, int K, float alpha,
-                                                        const float* __restrict__ bias, int relu, int accumulate) {
+                                                        const float* __restrict__ bias, int relu, int accumulate, int k_per_split) {
     __shared__ float As[16][64 + 4];
     __shared__ float Bs[16][64 + 4];
     const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
     const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    const int kb = blockIdx.z * k_per_split;
+    const int ke = min(K, kb + k_per_split);
     float acc[4][4] = {};
-    for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int k0 = kb; k0 < ke; k0 += 16) {
         for (int i = threadIdx.x; i < 64 * 16; i += 256) {
-            const int kk = i % 16, mm = i / 16;
+            // consecutive threads walk the contiguous dimension of each operand
+            int kk, mm;
+            if (sak == 1) { kk = i % 16; mm = i / 16; } else { mm = i % 64; kk = i / 64; }
             const int gm = m0 + mm, gk = k0 + kk;
-            As[kk][mm] = (gm < M && gk < K) ? A[gm * sam + gk * sak] : 0.f;
-            const int gn = n0 + mm;
-            Bs[kk][mm] = (gn < N && gk < K) ? B[gk * sbk + gn * sbn] : 0.f;
+            As[kk][mm] = (gm < M && gk < ke) ? A[gm * sam + gk * sak] : 0.f;
+            if (sbk == 1) { kk = i % 16; mm = i / 16; } else { mm = i % 64; kk = i / 64; }
+            const int gn = n0 + mm, gk2 = k0 + kk;
+            Bs[kk][mm] = (gn < N && gk2 < ke) ? B[gk2 * sbk + gn * sbn] : 0.f;
         }
         __syncthreads();
 #pragma unroll
@@ -594,6 +599,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const float* __restrict_
             const int gn = n0 + tx * 4 + j;
             if (gn >= N) continue;
             float v = alpha * acc[i][j];
+            if (gridDim.z > 1) { atomicAdd(C + gm * ldc + gn, v); continue; }   // split-K (accumulate only)
             if (bias != nullptr) v += bias[gn];
             if (accumulate) v += C[gm * ldc + gn];
             if (relu) v = fmaxf(v, 0.f);
@@ -815,7 +821,17 @@ extern "C" int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, con
     // op(A)[m][k]: transA ? A[k*lda+m] : A[m*lda+k];  op(B)[k][n]: transB ? B[n*ldb+k] : B[k*ldb+n]
     const long long sam = transA ? 1 : lda, sak = transA ? lda : 1;
     const long long sbk = transB ? 1 : ldb, sbn = transB ? ldb : 1;
-    dim3 grid((N + 63) / 64, (M + 63) / 64);
-    gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate);
+    dim3 grid((N + 63) / 64, (M + 63) / 64, 1);
+    int k_per_split = K;
+    if (accumulate && bias == nullptr && !relu && K >= 1024) {   // split-K keeps the SMs busy on wgrad-shaped problems
+        const int blocks = grid.x * grid.y;
+        int splits = (148 * 2 + blocks - 1) / blocks;
+        if (splits > K / 256) splits = K / 256;
+        if (splits > 1) {
+            k_per_split = ((K + splits - 1) / splits + 15) / 16 * 16;
+            grid.z = (K + k_per_split - 1) / k_per_split;
+        }
+    }
+    gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate, k_per_split);
     LAUNCH_OK();
 }

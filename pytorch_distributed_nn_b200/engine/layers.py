@@ -254,7 +254,11 @@ class BatchNorm(Layer):
                      stats=self.stats, mean_invstd=self.mean_invstd, out=self.y)
         return self.y
 
-    def backward(self, dy, want_dresidual=False):
+    def backward(self, dy):
+        return self.backward_res(dy, False)[0]
+
+    def backward_res(self, dy, want_dresidual=False):
+        """Returns (dx, dresidual): dresidual is the gradient w.r.t. the tensor added before the ReLU."""
         if want_dresidual and self.dres is None:
             self.dres = torch.empty_like(self.dx)
         F.bn_backward(self.x, self.y, dy, self.weight.wf, self.mean_invstd, relu=self.relu,
@@ -440,15 +444,15 @@ class BasicBlock(Layer):
         return self.bn2.forward(o2, residual=s)
 
     def backward(self, dy):
-        do2, dres = self.bn2.backward(dy, want_dresidual=True)
+        do2, dres = self.bn2.backward_res(dy, True)
         if self.has_sc:
             # shortcut parameters sit after bn2 in parameters() order: their gradients leave first
-            dso, _ = self.sc_bn.backward(dres)
+            dso = self.sc_bn.backward(dres)
             dxs = self.sc_conv.backward(dso)
         else:
             dxs = dres
         da1 = self.conv2.backward(do2)
-        do1, _ = self.bn1.backward(da1)
+        do1 = self.bn1.backward(da1)
         return self.conv1.backward(do1, dx_residual=dxs)
 
 
@@ -496,14 +500,14 @@ class Bottleneck(Layer):
         return self.bn3.forward(o3, residual=s)
 
     def backward(self, dy):
-        do3, dres = self.bn3.backward(dy, want_dresidual=True)
+        do3, dres = self.bn3.backward_res(dy, True)
         if self.has_sc:
-            dso, _ = self.sc_bn.backward(dres)
+            dso = self.sc_bn.backward(dres)
             dxs = self.sc_conv.backward(dso)
         else:
             dxs = dres
         da2 = self.conv3.backward(do3)
-        do2, _ = self.bn2.backward(da2)
+        do2 = self.bn2.backward(da2)
         da1 = self.conv2.backward(do2)
-        do1, _ = self.bn1.backward(da1)
+        do1 = self.bn1.backward(da1)
         return self.conv1.backward(do1, dx_residual=dxs)

@@ -1,0 +1,215 @@
+"""Device-resident synchronous-SGD parameter server (the B200 backend).
+
+Role model (reference: rank 0 = master holding the weights, ranks >= 1 = workers, pytorch_code/distributed_nn.py:91-102):
+
+* ``colocate=False``  rank 0 is master-only, ranks 1..G-1 are the n = G-1 workers (reference semantics).
+* ``colocate=True``   GPU 0 additionally hosts a worker, so n = G (and G = 1 is a complete system: one
+                      master + one worker sharing a stream). This is what the throughput bench uses.
+
+Per step s (1-based, as ``STEP_START_`` in the reference):
+
+  worker  wait(ready >= s) -> prepare derived weight layouts -> [injected delay] -> forward -> loss ->
+          backward; each finished gradient bucket is pushed (bf16 or fp32) into the master's slot for this
+          worker by ``pdnn_ps_push``; the last bucket's push publishes ``arrival[w] = s``.
+  master  ``pdnn_ps_master_step``: one kernel polls the arrival flags, takes the first k complete sets, stores
+          ``closed = s`` into every late worker's memory (their remaining kernels become no-ops and their push
+          is dropped), reduces the selected slots, applies 1/k + momentum SGD on the fp32 master weights,
+          casts and stores the new weights into every worker's weight buffer and finally ``ready = s+1``.
+
+Nothing in the step touches the host: each rank simply enqueues its kernels; streams block on device flags.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+from typing import Callable, Optional
+
+import torch
+
+from ..engine.network import Network, build_network
+from ..ops import _lib
+from ..ops import functional as F
+from .peer import PeerArena
+from .protocol import AVG_MODES, STEP_START_
+
+U32 = 4
+FLAG_WORDS = 256          # per-rank flag block (uint32 words)
+W_READY, W_CLOSED, W_STEP = 0, 1, 2         # worker-side words
+M_ARRIVAL, M_CONTROL, M_RESULT = 32, 64, 128  # master-side words (arrival[n], control[64], result[4])
+
+
+class B200ParameterServer:
+    """One instance per rank. Builds the engine network, the peer arena and drives the step loop."""
+
+    def __init__(self, network: str, batch_size: int, rank: int = 0, world_size: int = 1, *, lr: float = 0.01,
+                 momentum: float = 0.0, num_aggregate: Optional[int] = None, avg_mode: str = "k",
+                 grad_dtype: str = "bf16", colocate: bool = True, n_buckets: int = 8, seed: int = 0,
+                 deadline_ms: float = 0.0, delay_fn: Optional[Callable[[int, int], int]] = None, group=None,
+                 device=None):
+        assert torch.cuda.is_available(), "the b200 backend needs a GPU (use --backend gloo on CPU)"
+        self.rank, self.world = rank, world_size
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.colocate = colocate or world_size == 1
+        self.n_workers = world_size if self.colocate else world_size - 1
+        assert 1 <= self.n_workers <= _lib.MAX_WORKERS
+        self.is_master = rank == 0
+        self.worker_id = rank if self.colocate else rank - 1          # -1 on a master-only rank
+        self.is_worker = self.worker_id >= 0
+        self.k = self.n_workers if not num_aggregate else min(int(num_aggregate), self.n_workers)
+        self.lr, self.mu = float(lr), float(momentum)
+        self.avg_mode = AVG_MODES[avg_mode]
+        self.grad_bf16 = grad_dtype == "bf16"
+        self.deadline_ns = int(deadline_ms * 1e6)
+        self.delay_fn = delay_fn
+        self.step = STEP_START_
+        self.batch_size = batch_size
+
+        # ---- network (every rank builds it: the master needs the layout, workers need the layers)
+        self.net: Network = self._build(network, batch_size, n_buckets, group)
+        net = self.net
+        if self.is_master:
+            net.init_parameters(seed)          # fills w32 and (through sync_compute_weights) the local w
+            self.momentum = torch.zeros(net.total, device=self.device, dtype=torch.float32)
+        self._install_hooks()
+        self._initial_broadcast(group)
+
+    # ---- construction ---------------------------------------------------------------------------
+    def _build(self, network, batch, n_buckets, group) -> Network:
+        # a meta-device pass gives the flat layout (size, dtype) without allocating anything
+        proto = build_network(network, 128, device="meta", n_buckets=n_buckets)
+        total, wdtype = proto.total, proto.dtype
+        del proto
+        self.wbytes = total * (2 if wdtype == torch.bfloat16 else 4)
+        self.slot_elem = 2 if self.grad_bf16 else 4
+        slot_bytes = total * self.slot_elem
+        # symmetric size keeps the carve offsets identical on every rank (only rank 0's slots are used)
+        arena_bytes = 4096 + FLAG_WORDS * U32 + self.wbytes + 512 + self.n_workers * (slot_bytes + 256)
+        self.arena = PeerArena(arena_bytes, self.rank, self.world, self.device, group)
+        self.off_flags = self.arena.carve(FLAG_WORDS * U32)
+        self.off_w = self.arena.carve(self.wbytes)
+        self.off_slots = [self.arena.carve(slot_bytes) for _ in range(self.n_workers)]
+        self.flags = self.arena.tensor(self.off_flags, FLAG_WORDS * U32, torch.int32)
+        w_ext = self.arena.tensor(self.off_w, self.wbytes, wdtype)
+        real_batch = batch if self.is_worker else self._min_batch(network)
+        return build_network(network, real_batch, device=self.device, n_buckets=n_buckets, external_w=w_ext)
+
+    @staticmethod
+    def _min_batch(network):
+        return 32
+
+    def _flag_ptr(self, rank, word):
+        return self.arena.ptr(rank, self.off_flags + word * U32)
+
+    def _worker_rank(self, w):
+        return w if self.colocate else w + 1
+
+    def _install_hooks(self):
+        net = self.net
+        self.closed_word = self.flags[W_CLOSED: W_CLOSED + 1]
+        self.step_word = self.flags[W_STEP: W_STEP + 1]
+        if self.is_worker:
+            w = self.worker_id
+            self._slot_ptr = self.arena.ptr(0, self.off_slots[w])          # my slot lives on the master (rank 0)
+            self._arrival_ptr = self._flag_ptr(0, M_ARRIVAL + w)
+            last_bucket = net.buckets[-1].index
+
+            def on_bucket(b):
+                flag = self._arrival_ptr if b.index == last_bucket else None
+                _lib.call("pdnn_ps_push", net.g.data_ptr() + b.start * 4, self._slot_ptr + b.start * self.slot_elem,
+                          b.end - b.start, int(self.grad_bf16), flag, self.step,
+                          self.closed_word.data_ptr(), self.step_word.data_ptr(), 0, _lib.stream_ptr())
+
+            net.on_bucket = on_bucket
+        if self.is_master:
+            m = _lib.PSMaster()
+            for w in range(self.n_workers):
+                r = self._worker_rank(w)
+                m.slots[w] = self.arena.ptr(0, self.off_slots[w])
+                m.worker_weights[w] = self.arena.ptr(r, self.off_w)
+                m.worker_ready[w] = self._flag_ptr(r, W_READY)
+                m.worker_closed[w] = self._flag_ptr(r, W_CLOSED)
+            m.arrival_flags = self._flag_ptr(0, M_ARRIVAL)
+            m.multicast_weights = None
+            m.master_w = net.w32.data_ptr()
+            m.momentum = self.momentum.data_ptr()
+            m.control = self._flag_ptr(0, M_CONTROL)
+            m.n = net.total
+            m.n_workers = self.n_workers
+            m.k = self.k
+            m.slot_is_bf16 = int(self.grad_bf16)
+            m.weights_are_bf16 = int(net.w.dtype == torch.bfloat16)
+            m.avg_mode = self.avg_mode
+            m.lr, m.mu = self.lr, self.mu
+            m.deadline_ns = self.deadline_ns
+            m.max_ctas = 0
+            self._margs = m
+            self.result = self.flags[M_RESULT: M_RESULT + 4]
+            self.history = []
+
+    def _initial_broadcast(self, group):
+        """Step-1 weights: the master stores its initial weights into every worker buffer and releases them
+        (reference: first async_bcast_step + weight Bcast, sync_replicas_master_nn.py:121-140)."""
+        net = self.net
+        if self.is_master:
+            src = net.w32
+            for w in range(self.n_workers):
+                r = self._worker_rank(w)
+                dst = self.arena.ptr(r, self.off_w)
+                if r == 0:
+                    continue                      # init_parameters already filled the local compute copy
+                if net.w.dtype == torch.bfloat16:
+                    _lib.call("pdnn_cast_f32_to_bf16", src, dst, net.total, _lib.stream_ptr())
+                else:
+                    _lib.call("pdnn_p2p_copy", src, dst, net.total * 4, 0, _lib.stream_ptr())
+            for w in range(self.n_workers):
+                _lib.call("pdnn_set_word", self._flag_ptr(self._worker_rank(w), W_READY), STEP_START_, _lib.stream_ptr())
+        torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=group)
+
+    # ---- step loop ------------------------------------------------------------------------------
+    def worker_step(self, x_nchw_f32, labels):
+        """Enqueue one worker step (no host synchronisation). Returns the device loss tensor."""
+        net = self.net
+        st = _lib.stream_ptr()
+        _lib.call("pdnn_ps_wait_flag", self.flags.data_ptr() + W_READY * U32, self.step, self.step_word.data_ptr(), 0, st)
+        F.set_abort_guard(self.closed_word, self.step_word)
+        try:
+            net.prepare()
+            if self.delay_fn is not None:
+                ns = int(self.delay_fn(self.worker_id, self.step))
+                if ns > 0:
+                    _lib.call("pdnn_delay", ns, self.closed_word.data_ptr(), self.step_word.data_ptr(), st)
+            loss = net.train_step(x_nchw_f32, labels)
+        finally:
+            F.set_abort_guard(None, None)
+        return loss
+
+    def master_step(self):
+        """Enqueue the master's aggregate/update/broadcast kernel for the current step."""
+        m = self._margs
+        m.step = self.step
+        _lib.call("pdnn_ps_master_step", C.byref(m), self.result.data_ptr(), _lib.stream_ptr())
+
+    def train_step(self, x_nchw_f32=None, labels=None):
+        """One synchronous-SGD step of this rank's role(s); advances the step counter."""
+        loss = None
+        if self.is_worker:
+            loss = self.worker_step(x_nchw_f32, labels)
+        if self.is_master:
+            self.master_step()
+        self.step += 1
+        return loss
+
+    def last_result(self):
+        """(selected_mask, kill_mask, n_received, step) of the most recent master step (synchronises)."""
+        r = self.result.cpu().tolist()
+        return tuple(int(v) & 0xFFFFFFFF for v in r)
+
+    def master_state_dict(self):
+        return self.net.state_dict()
+
+    def close(self):
+        torch.cuda.synchronize()
+        self.arena.close()
