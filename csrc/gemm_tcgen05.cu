@@ -27,7 +27,9 @@ constexpr int BLOCK_K = 64;   // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 256;
 
-enum OperMode : int { OP_K2D = 0, OP_MN2D = 1, OP_CONVK = 2, OP_CONVMN = 3 };
+// OP_CONVMN_G3: wgrad B operand = the three s-shifts of one filter row side by side (N = 3 x 64 channels), so the
+// dY tile is fetched once per three shifts (used when Cin <= 128, where a single-shift N tile starves the MMA).
+enum OperMode : int { OP_K2D = 0, OP_MN2D = 1, OP_CONVK = 2, OP_CONVMN = 3, OP_CONVMN_G3 = 4 };
 
 struct GemmParams {
     int M, N, K;
@@ -177,6 +179,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int j = 0; j < BN / 64; ++j)
                             tma_load_4d(sb + j * 8192, &tmB, fb, b_c0 + j * 64, b_s - p.pad,
                                         h0 + b_r - p.pad, n0);
+                    } else if (BMODE == OP_CONVMN_G3) {
+                        const int p0 = kit * BLOCK_K;
+                        const int n0 = p0 / hw;
+                        const int h0 = (p0 - n0 * hw) / p.W;
+                        const int r = nt / p.cblks;
+                        const int cb = nt - r * p.cblks;
+#pragma unroll
+                        for (int j = 0; j < 3; ++j)
+                            tma_load_4d(sb + j * 8192, &tmB, fb, cb * 64, j - p.pad, h0 + r - p.pad, n0);
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -185,7 +196,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         constexpr uint32_t A_MN = (AMODE == OP_MN2D) ? 1u : 0u;
-        constexpr uint32_t B_MN = (BMODE == OP_MN2D || BMODE == OP_CONVMN) ? 1u : 0u;
+        constexpr uint32_t B_MN = (BMODE == OP_MN2D || BMODE == OP_CONVMN || BMODE == OP_CONVMN_G3) ? 1u : 0u;
         constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
         int stage = 0;
         uint32_t phase = 0;
@@ -241,7 +252,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 uint32_t v[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + acc * BN + c * 32, v);
                 tmem_ld_wait();
-                const int col0 = nt * BN + c * 32;
+                int col0 = nt * BN + c * 32;
+                if (BMODE == OP_CONVMN_G3) {   // tile columns = (shift s, 64 channels); output columns are KRSC
+                    const int r = nt / p.cblks;
+                    const int cb = nt - r * p.cblks;
+                    const int j = c * 32;
+                    col0 = (r * p.S + (j >> 6)) * p.C + cb * 64 + (j & 63);
+                }
                 if (!row_ok || col0 >= p.N) continue;
                 float f[32];
 #pragma unroll
@@ -559,7 +576,8 @@ extern "C" int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, in
                  "conv_wgrad: %dx%d images (batch %d) do not tile into 64-pixel boxes", H, W, batch);
     const long long pix = (long long)batch * H * W;
     PDNN_REQUIRE(pix % BLOCK_K == 0 && pix < (1ll << 31), "conv_wgrad: pixel count must be a multiple of 64");
-    const int bn = (C % 256 == 0) ? 256 : (C % 128 == 0 ? 128 : 64);
+    const bool g3 = (S == 3 && C <= 128);
+    const int bn = g3 ? 192 : ((C % 256 == 0) ? 256 : (C % 128 == 0 ? 128 : 64));
     CUtensorMap tmA, tmB;
     {
         long long ad[2] = {Kout, pix};
@@ -573,12 +591,18 @@ extern "C" int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, in
     }
     p.M = Kout; p.N = R * S * C; p.K = (int)pix;
     p.m_tiles = (Kout + BLOCK_M - 1) / BLOCK_M;
-    p.cblks = C / bn;
-    p.n_tiles = R * S * p.cblks;
+    if (g3) {
+        p.cblks = C / 64;
+        p.n_tiles = R * p.cblks;
+    } else {
+        p.cblks = C / bn;
+        p.n_tiles = R * S * p.cblks;
+    }
     p.k_iters_total = (int)(pix / BLOCK_K);
     p.H = H; p.W = W; p.C = C; p.R = R; p.S = S; p.pad = pad;
     fill_epilogue(p, epi);
     p.k_splits = choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits);
     finish_splits(p);
+    if (g3) return launch_gemm<OP_MN2D, OP_CONVMN_G3, 192>(tmA, tmB, p, epi->max_ctas, stream);
     return dispatch_bn<OP_MN2D, OP_CONVMN>(bn, tmA, tmB, p, epi->max_ctas, stream);
 }

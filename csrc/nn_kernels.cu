@@ -145,6 +145,70 @@ __global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     }
 }
 
+// stem-style im2col (C < 8): one thread produces 8 consecutive k of one row with a single 16-byte store.
+__global__ void im2col_rows8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int H, int W, int C,
+                                    int R, int S, int stride, int pad, int OH, int OW, int Kpad) {
+    const int K = R * S * C;
+    const int k8n = Kpad / 8;
+    const long long total = (long long)N * OH * OW * k8n;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int k8 = (int)(i % k8n);
+        const long long m = i / k8n;
+        const int ow = (int)(m % OW);
+        const int oh = (int)((m / OW) % OH);
+        const int n = (int)(m / ((long long)OW * OH));
+        __nv_bfloat16 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int k = k8 * 8 + j;
+            __nv_bfloat16 e = __float2bfloat16(0.f);
+            if (k < K) {
+                const int c = k % C;
+                const int rs = k / C;
+                const int s = rs % S, r = rs / S;
+                const int h = oh * stride - pad + r, w = ow * stride - pad + s;
+                if (h >= 0 && h < H && w >= 0 && w < W) e = x[(((long long)n * H + h) * W + w) * C + c];
+            }
+            v[j] = e;
+        }
+        *reinterpret_cast<uint4*>(col + m * Kpad + k8 * 8) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
+// vectorised col2im: C % 8 == 0, one thread gathers 8 channels of one input pixel (16-byte loads).
+__global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C,
+                                   int R, int S, int stride, int pad, int OH, int OW, int Kpad) {
+    const int C8 = C / 8;
+    const long long total = (long long)N * H * W * C8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % C8);
+        const long long pix = i / C8;
+        const int w = (int)(pix % W);
+        const int h = (int)((pix / W) % H);
+        const int n = (int)(pix / ((long long)W * H));
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int r = 0; r < R; ++r) {
+            const int hh = h + pad - r;
+            if (hh < 0 || hh % stride != 0) continue;
+            const int oh = hh / stride;
+            if (oh >= OH) continue;
+            for (int s = 0; s < S; ++s) {
+                const int ww = w + pad - s;
+                if (ww < 0 || ww % stride != 0) continue;
+                const int ow = ww / stride;
+                if (ow >= OW) continue;
+                float v[8];
+                load8(dcol + (((long long)n * OH + oh) * OW + ow) * Kpad + (r * S + s) * C + c8 * 8, v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += v[j];
+            }
+        }
+        store8(dx + pix * C + c8 * 8, acc);
+    }
+}
+
 template <typename T>
 __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, int N, int H, int W, int C, int R, int S,
                               int stride, int pad, int OH, int OW, int Kpad) {
@@ -231,36 +295,40 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
     }
 }
 
+// Apply passes: every thread keeps ONE 8-channel group for its whole life (scale/shift are computed once per
+// thread, not once per element) and walks rows with a stride of (rows per block) x (grid size).
 __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
                                                            float* __restrict__ mean_invstd, float* running_mean, float* running_var,
                                                            long long M, int C, float eps, float momentum, int relu) {
     const int tpr = C / 8;
+    const int rpi = max(1, (int)blockDim.x / tpr);
+    const int ct = threadIdx.x % tpr;
+    const int rgrp = threadIdx.x / tpr;
+    if (rgrp >= rpi) return;
     const float invM = 1.f / (float)M;
-    const long long total = M * tpr;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int ct = (int)(i % tpr);
-        const long long row = i / tpr;
-        float sc[8], sf[8];
+    float sc[8], sf[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = ct * 8 + j;
-            const float mean = stats[c] * invM;
-            const float var = fmaxf(stats[C + c] * invM - mean * mean, 0.f);
-            const float inv = rsqrtf(var + eps);
-            sc[j] = gamma[c] * inv;
-            sf[j] = beta[c] - mean * sc[j];
-            if (row == 0) {
-                mean_invstd[c] = mean;
-                mean_invstd[C + c] = inv;
-                if (running_mean != nullptr) {
-                    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-                    const float unbiased = M > 1 ? var * (float)M / (float)(M - 1) : var;
-                    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-                }
+    for (int j = 0; j < 8; ++j) {
+        const int c = ct * 8 + j;
+        const float mean = stats[c] * invM;
+        const float var = fmaxf(stats[C + c] * invM - mean * mean, 0.f);
+        const float inv = rsqrtf(var + eps);
+        sc[j] = gamma[c] * inv;
+        sf[j] = beta[c] - mean * sc[j];
+        if (blockIdx.x == 0 && rgrp == 0) {
+            mean_invstd[c] = mean;
+            mean_invstd[C + c] = inv;
+            if (running_mean != nullptr) {
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                const float unbiased = M > 1 ? var * (float)M / (float)(M - 1) : var;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
             }
         }
+    }
+    const long long rstride = (long long)gridDim.x * rpi;
+    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride) {
         const long long off = row * C + ct * 8;
         float v[8];
         load8(x + off, v);
@@ -286,11 +354,25 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
                                                            __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu) {
     const int tpr = C / 8;
+    const int rpi = max(1, (int)blockDim.x / tpr);
+    const int ct = threadIdx.x % tpr;
+    const int rgrp = threadIdx.x / tpr;
+    if (rgrp >= rpi) return;
     const float invM = 1.f / (float)M;
-    const long long total = M * tpr;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int ct = (int)(i % tpr);
-        const long long row = i / tpr;
+    // dx = a*dz + b*x + c0 with a = gamma*inv, b = -a*inv*s1/M, c0 = -a*s0/M - b*mean
+    float ka[8], kb[8], kc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = ct * 8 + j;
+        const float mean = mean_invstd[c], inv = mean_invstd[C + c];
+        const float s0 = sums[c], s1 = sums[C + c];
+        ka[j] = gamma[c] * inv;
+        kb[j] = -ka[j] * inv * s1 * invM;
+        kc[j] = -ka[j] * s0 * invM - kb[j] * mean;
+        if (blockIdx.x == 0 && rgrp == 0) { dgamma[c] = s1; dbeta[c] = s0; }
+    }
+    const long long rstride = (long long)gridDim.x * rpi;
+    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride) {
         const long long off = row * C + ct * 8;
         float xv[8], dv[8];
         load8(x + off, xv);
@@ -304,14 +386,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
         if (dres != nullptr) store8(dres + off, dv);
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int c = ct * 8 + j;
-            const float mean = mean_invstd[c], inv = mean_invstd[C + c];
-            const float s0 = sums[c], s1 = sums[C + c];
-            const float xhat = (xv[j] - mean) * inv;
-            o[j] = gamma[c] * inv * (dv[j] - s0 * invM - xhat * s1 * invM);
-            if (row == 0) { dgamma[c] = s1; dbeta[c] = s0; }
-        }
+        for (int j = 0; j < 8; ++j) o[j] = ka[j] * dv[j] + kb[j] * xv[j] + kc[j];
         store8(dx + off, o);
     }
 }
@@ -652,6 +727,9 @@ extern "C" int pdnn_im2col_bf16(const void* x, void* col, int N, int H, int W, i
     if (C % 8 == 0 && Kpad == R * S * C) {
         const long long total = (long long)N * OH * OW * R * S * (C / 8);
         im2col_vec8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW);
+    } else if (Kpad % 8 == 0) {
+        const long long total = (long long)N * OH * OW * (Kpad / 8);
+        im2col_rows8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
     } else {
         const long long total = (long long)N * OH * OW * Kpad;
         im2col_kernel<__nv_bfloat16><<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
@@ -666,7 +744,10 @@ extern "C" int pdnn_im2col_f32(const float* x, float* col, int N, int H, int W, 
 }
 extern "C" int pdnn_col2im_bf16(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
                                 int OW, int Kpad, void* stream) {
-    col2im_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * C, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    if (C % 8 == 0 && Kpad % 8 == 0)
+        col2im_vec8_kernel<<<grid_for((long long)N * H * W * (C / 8), 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+    else
+        col2im_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * C, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
     LAUNCH_OK();
 }
 extern "C" int pdnn_col2im_f32(const float* dcol, float* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
@@ -692,8 +773,10 @@ extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C
 extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
                                  void* y, float* mean_invstd, float* running_mean, float* running_var, long long M, int C,
                                  float eps, float momentum, int relu, void* stream) {
-    PDNN_REQUIRE(C % 8 == 0, "bn: C=%d must be a multiple of 8", C);
-    bn_fwd_apply_kernel<<<grid_for(M * (C / 8), 256, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
+    PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
+    int rpi_a; size_t smem_a;
+    bn_reduce_cfg(C, &rpi_a, &smem_a);
+    bn_fwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
                                                                                      running_mean, running_var, M, C, eps, momentum, relu);
     LAUNCH_OK();
 }
@@ -709,7 +792,10 @@ extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, 
 extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,
                                  const float* sums, void* dx, void* dresidual, float* dgamma, float* dbeta, long long M, int C,
                                  int relu, void* stream) {
-    bn_bwd_apply_kernel<<<grid_for(M * (C / 8), 256, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
+    PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
+    int rpi_a; size_t smem_a;
+    bn_reduce_cfg(C, &rpi_a, &smem_a);
+    bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
                                                                                      BF(dresidual), dgamma, dbeta, M, C, relu);
     LAUNCH_OK();
 }

@@ -117,6 +117,7 @@ class Conv2d(Layer):
         if self.mode == "implicit" and not first:
             self.w_t = torch.empty(cin, k, k, cout, device=dev, dtype=dt)
         self.x = None
+        self._colbuf = None
 
     @staticmethod
     def _tileable(n, h, w):
@@ -164,11 +165,20 @@ class Conv2d(Layer):
                         out=self.y.view(-1, self.cout), bias=bias)
         return self.y
 
-    def _col(self, x):
+    def _col(self, x, reuse=False):
+        """im2col of x. The matrix is kept per layer (net.keep_col) so that backward does not rebuild it;
+        with keep_col off it lives in the shared scratch and is recomputed for wgrad."""
         if not self.lowered_copy:
             return x.view(-1, self.cin)
         m = self.out_shape[0] * self.oh * self.ow
-        col = self.net.scratch(m * self.kpad).view(m, self.kpad)
+        if self.net.keep_col:
+            if self._colbuf is None:
+                self._colbuf = torch.empty(m, self.kpad, device=self.net.device, dtype=self.net.dtype)
+            col = self._colbuf
+            if reuse:
+                return col
+        else:
+            col = self.net.scratch(m * self.kpad).view(m, self.kpad)
         F.im2col(x, self.k, self.k, self.stride, self.pad, k_pad=self.kpad, out=col)
         return col
 
@@ -184,7 +194,7 @@ class Conv2d(Layer):
         if self.mode == "implicit":
             F.conv_wgrad(x, dy, R=self.k, S=self.k, pad=self.pad, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
         elif self.mode == "lowered":
-            col = self._col(x)   # recomputed: cheaper than keeping 9x activations alive
+            col = self._col(x, reuse=True)
             if self.kpad != self.kdim:
                 self.dw_pad.zero_()
                 F.gemm(dy2, col, a_mn_major=True, b_mn_major=True, M=self.cout, N=self.kpad, K=m, out=self.dw_pad, accumulate=True)
@@ -193,7 +203,7 @@ class Conv2d(Layer):
                 F.gemm(dy2, col, a_mn_major=True, b_mn_major=True, M=self.cout, N=self.kdim, K=m,
                        out=self.weight.g.view(self.cout, self.kdim), accumulate=True)
         else:
-            col = self._col(x)
+            col = self._col(x, reuse=True)
             F.gemm_simt(dy2, col, trans_a=True, M=self.cout, N=self.kdim, K=m, out=self.weight.g.view(self.cout, self.kdim), accumulate=True)
         if self.bias is not None:
             F.col_sum(dy2, out=self.bias.g, accumulate=True)

@@ -53,6 +53,7 @@ class Network:
         self.correct = torch.zeros(1, device=self.device, dtype=torch.int32)
         self.dlogits = None
         self.x_in = None
+        self.keep_col = True   # keep im2col matrices of lowered convs for backward (memory for time)
 
     # ---- construction ---------------------------------------------------------------------------
     def add(self, layer):
