@@ -1,0 +1,189 @@
+"""GPU: the B200 engine (forward, loss, all parameter gradients) vs the torch fp32 models; state_dict round trip;
+the parameter-server master kernel vs the k-of-n oracle."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _fp32_reference():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+
+
+@pytest.mark.parametrize("name,batch", [("LeNet", 32), ("MLP", 64)])
+def test_fp32_networks_match_torch_exactly(name, batch):
+    from _oracle import grad_report, l2_rel, make_batch, make_pair
+    net, ref = make_pair(name, batch)
+    x, y = make_batch(name, batch, False)
+    loss = net.train_step(x.flatten(1) if name == "MLP" else x, y)
+    out = ref(x)
+    rl = torch.nn.functional.cross_entropy(out, y)
+    rl.backward()
+    assert l2_rel(net.logits[:, :10], out) < 1e-5
+    assert abs(float(loss) - float(rl)) < 1e-5
+    for k, (cos, rel) in grad_report(net, ref).items():
+        assert cos > 0.99999 and rel < 1e-4, (k, cos, rel)
+
+
+@pytest.mark.parametrize("name,batch", [("ResNet18", 64), ("VGG11", 64), ("ResNet50", 32)])
+def test_bf16_networks_forward_and_teacher_forced_backward(name, batch):
+    from _oracle import grad_report, l2_rel, make_batch, make_pair, teacher_force
+    net, ref = make_pair(name, batch)
+    x, y = make_batch(name, batch, True)
+    loss = net.train_step(x, y)
+    teacher_force(net, ref)
+    out = ref(x)
+    rl = torch.nn.functional.cross_entropy(out, y)
+    rl.backward()
+    assert l2_rel(net.logits[:, :10], out) < 2e-2
+    assert abs(float(loss) - float(rl)) / float(rl) < 5e-3
+    rep = grad_report(net, ref)
+    bad = {k: v for k, v in rep.items() if v[0] < 0.995}
+    assert not bad, bad
+
+
+def test_state_dict_roundtrip_matches_torch_layout():
+    from pytorch_distributed_nn_b200.engine.network import build_network
+    from pytorch_distributed_nn_b200.models import build_model
+    for name in ("LeNet", "ResNet18", "VGG11"):
+        net = build_network(name, 32)
+        net.init_parameters(seed=3)
+        sd = net.state_dict()
+        ref = build_model(name)
+        rsd = ref.state_dict()
+        assert list(sd.keys()) == list(rsd.keys()), name
+        for k in sd:
+            assert tuple(sd[k].shape) == tuple(rsd[k].shape), (name, k)
+        net2 = build_network(name, 32)
+        net2.load_state_dict(sd)
+        assert torch.equal(net2.w32, net.w32)
+
+
+def test_training_reduces_loss_through_parameter_server():
+    from pytorch_distributed_nn_b200.parallel.b200_ps import B200ParameterServer
+    ps = B200ParameterServer("ResNet18", 32, 0, 1, lr=0.05, momentum=0.5)
+    x = torch.empty(32, 3, 32, 32, device="cuda").uniform_(0, 255)
+    y = torch.randint(0, 10, (32,), device="cuda")
+    losses = [float(ps.train_step(x, y)) for _ in range(6)]
+    assert losses[-1] < 0.5 * losses[0], losses
+    assert ps.last_result() == (1, 0, 1, 6)
+    ps.close()
+
+
+def test_ps_single_worker_update_equals_momentum_sgd():
+    from pytorch_distributed_nn_b200.parallel.b200_ps import B200ParameterServer
+    ps = B200ParameterServer("LeNet", 32, 0, 1, lr=0.1, momentum=0.9, grad_dtype="fp32")
+    net = ps.net
+    x = torch.randn(32, 1, 28, 28, device="cuda")
+    y = torch.randint(0, 10, (32,), device="cuda")
+    w = net.w32.clone()
+    m = torch.zeros_like(w)
+    for _ in range(3):
+        ps.train_step(x, y)
+        torch.cuda.synchronize()
+        g = net.g.clone()
+        m = 0.9 * m + g
+        w = w - 0.1 * m
+        assert torch.allclose(net.w32, w, rtol=1e-5, atol=1e-6)
+        assert torch.equal(net.w[: net.total], net.w32)      # fp32 network: broadcast copy == master copy
+    ps.close()
+
+
+def _master_args(n_workers, n, k, slots, flags, weights, ready, closed, master_w, mom, ctl, step, avg_mode=0, bf16_slots=False,
+                 lr=0.1, mu=0.5):
+    from pytorch_distributed_nn_b200.ops import _lib
+    m = _lib.PSMaster()
+    for w in range(n_workers):
+        m.slots[w] = slots[w].data_ptr()
+        m.worker_weights[w] = weights[w].data_ptr()
+        m.worker_ready[w] = ready.data_ptr() + 4 * w
+        m.worker_closed[w] = closed.data_ptr() + 4 * w
+    m.arrival_flags = flags.data_ptr()
+    m.multicast_weights = None
+    m.master_w = master_w.data_ptr()
+    m.momentum = mom.data_ptr()
+    m.control = ctl.data_ptr()
+    m.n, m.n_workers, m.k = n, n_workers, k
+    m.slot_is_bf16 = int(bf16_slots)
+    m.weights_are_bf16 = 1
+    m.avg_mode = avg_mode
+    m.lr, m.mu = lr, mu
+    m.step = step
+    m.deadline_ns = 0
+    m.max_ctas = 0
+    return m
+
+
+@pytest.mark.parametrize("avg_mode", ["k", "n"])
+def test_master_kernel_k_of_n_matches_oracle(avg_mode):
+    """All ranks' data on one GPU (the multi-rank path is emulated as ONE kernel over every worker's slot):
+    workers 0, 2, 3 of 4 have arrived for step 7, worker 1 carries a stale flag; k = 3."""
+    from pytorch_distributed_nn_b200.ops import _lib
+    from pytorch_distributed_nn_b200.parallel.oracle import kofn_update
+    from pytorch_distributed_nn_b200.parallel.protocol import AVG_MODES
+    n, nw, k, step = 100_003 // 4 * 4, 4, 3, 7
+    dev = "cuda"
+    grads = [torch.randn(n, device=dev) for _ in range(nw)]
+    flags = torch.tensor([7, 6, 7, 7], device=dev, dtype=torch.int32)
+    weights = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(nw)]
+    ready = torch.zeros(nw, device=dev, dtype=torch.int32)
+    closed = torch.zeros(nw, device=dev, dtype=torch.int32)
+    w0 = torch.randn(n, device=dev)
+    m0 = torch.randn(n, device=dev) * 0.1
+    master_w, mom = w0.clone(), m0.clone()
+    ctl = torch.zeros(64, device=dev, dtype=torch.int32)
+    result = torch.zeros(4, device=dev, dtype=torch.int32)
+    args = _master_args(nw, n, k, grads, flags, weights, ready, closed, master_w, mom, ctl, step, AVG_MODES[avg_mode])
+    _lib.call("pdnn_ps_master_step", C.byref(args), result.data_ptr(), _lib.stream_ptr())
+    torch.cuda.synchronize()
+    sel, kill, nrecv, st = [int(v) for v in result.tolist()]
+    assert (sel, kill, nrecv, st) == (0b1101, 0b0010, 3, 7)
+    assert closed.tolist() == [0, 7, 0, 0]                 # only the straggler is told to abandon step 7
+    assert ready.tolist() == [8, 8, 8, 8]                  # everybody is released into step 8
+    w_ref, m_ref, selected, killed = kofn_update(w0.cpu(), m0.cpu(), {i: g.cpu() for i, g in enumerate(grads)}, [0, 2, 3], k, nw,
+                                                 lr=0.1, mu=0.5, avg_mode=avg_mode)
+    assert selected == [0, 2, 3] and killed == [1]
+    assert torch.allclose(master_w.cpu(), w_ref, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(mom.cpu(), m_ref, rtol=1e-5, atol=1e-6)
+    for w in weights:
+        assert torch.equal(w, master_w.bfloat16())
+
+
+def test_push_kernel_casts_and_flags():
+    from pytorch_distributed_nn_b200.ops import _lib
+    n = 50_000
+    g = torch.randn(n, device="cuda")
+    slot = torch.zeros(n, device="cuda", dtype=torch.bfloat16)
+    flag = torch.zeros(1, device="cuda", dtype=torch.int32)
+    _lib.call("pdnn_ps_push", g, slot, n, 1, flag, 5, None, None, 0, _lib.stream_ptr())
+    torch.cuda.synchronize()
+    assert int(flag) == 5 and torch.equal(slot, g.bfloat16())
+    # a worker whose step was closed drops its push: slot and flag stay untouched
+    closed = torch.tensor([6], device="cuda", dtype=torch.int32)
+    stepw = torch.tensor([6], device="cuda", dtype=torch.int32)
+    slot2 = torch.zeros_like(slot)
+    _lib.call("pdnn_ps_push", g, slot2, n, 1, flag, 6, closed, stepw, 0, _lib.stream_ptr())
+    torch.cuda.synchronize()
+    assert int(flag) == 5 and float(slot2.float().abs().max()) == 0.0
+
+
+def test_delay_kernel_busy_waits_and_aborts():
+    from pytorch_distributed_nn_b200.ops import _lib
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    _lib.call("pdnn_delay", 20_000_000, None, None, _lib.stream_ptr())
+    e.record()
+    torch.cuda.synchronize()
+    assert 19.0 < s.elapsed_time(e) < 40.0
+    closed = torch.tensor([3], device="cuda", dtype=torch.int32)
+    stepw = torch.tensor([3], device="cuda", dtype=torch.int32)
+    s.record()
+    _lib.call("pdnn_delay", 200_000_000, closed, stepw, _lib.stream_ptr())
+    e.record()
+    torch.cuda.synchronize()
+    assert s.elapsed_time(e) < 20.0
