@@ -921,3 +921,65 @@ extern "C" int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, con
     gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate, k_per_split);
     LAUNCH_OK();
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free BatchNorm forward
+// ------------------------------------------------------------------------------------------------
+// pdnn_bn_fwd_stats + pdnn_bn_fwd_apply need a [2][C] fp32 statistics buffer that somebody has to allocate
+// and zero. Some users of this C ABI have no way to do that at the point where they call us: a plain-C host
+// that links the library without any device allocator of its own, a process in which another runtime has
+// already reserved all of HBM for its private pool (a raw cudaMalloc then fails), or a step loop that must
+// not stall on the device-wide synchronisation an allocation can imply. For them the statistics live in the
+// fixed device array below. It is sized for PDNN_BN_NOALLOC_MAX_C channels (2 x 2048 floats = 16 KiB) and
+// every GPU that loads this library keeps it until the process exits.
+//
+// The array name is only a host-side handle: kernels must be given the device address, which
+// cudaGetSymbolAddress returns for the device that is current at the time. The address is looked up once per
+// device, on that device's first call (so make that first call outside any stream capture), and cached.
+// All calls on a device share the one array and it keeps whatever the previous call left in it, so the part
+// that is used is cleared at the start of every call; two calls that overlap on the same GPU (different
+// streams) would race on it and must be serialised by the caller.
+#define PDNN_BN_NOALLOC_MAX_C 2048
+static __device__ __align__(256) float g_bn_noalloc_stats[2 * PDNN_BN_NOALLOC_MAX_C];
+
+#include <mutex>
+static float* g_bn_noalloc_ptr[64] = {nullptr};
+static std::mutex g_bn_noalloc_mutex;
+
+static int bn_noalloc_scratch(float** out) {
+    int dev = -1;
+    PDNN_CUDA_CHECK(cudaGetDevice(&dev));
+    PDNN_REQUIRE(dev >= 0 && dev < 64, "bn_fwd_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_bn_noalloc_mutex);
+    if (g_bn_noalloc_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        PDNN_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_bn_noalloc_stats));   // address on the CURRENT device
+        PDNN_REQUIRE(p != nullptr, "bn_fwd_noalloc: cudaGetSymbolAddress returned a null address");
+        g_bn_noalloc_ptr[dev] = p;
+    }
+    *out = g_bn_noalloc_ptr[dev];
+    return 0;
+}
+
+extern "C" int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const float* beta, const void* residual, void* y,
+                                   float* mean_invstd, float* running_mean, float* running_var, long long M, int C,
+                                   float eps, float momentum, int relu, void* stream) {
+    PDNN_REQUIRE(C > 0 && C % 8 == 0, "bn_fwd_noalloc: C=%d must be a positive multiple of 8", C);
+    PDNN_REQUIRE(C <= PDNN_BN_NOALLOC_MAX_C,
+                 "bn_fwd_noalloc: C=%d exceeds the built-in scratch (max %d channels); use pdnn_bn_fwd_stats/apply with "
+                 "your own [2][C] buffer", C, PDNN_BN_NOALLOC_MAX_C);
+    PDNN_REQUIRE(M > 0 && x != nullptr && y != nullptr && mean_invstd != nullptr, "bn_fwd_noalloc: null or empty arguments");
+    float* stats = nullptr;
+    if (int rc = bn_noalloc_scratch(&stats)) return rc;
+    // the array still holds the sums of the previous call: zero the [2][C] prefix this call uses
+    PDNN_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)C, ST(stream)));
+    int rpi; size_t smem;
+    bn_reduce_cfg(C, &rpi, &smem);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    bn_fwd_apply_kernel<<<grid_for((M + rpi - 1) / rpi, 1, 148 * 8), 256, 0, ST(stream)>>>(
+        CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd, running_mean, running_var, M, C, eps, momentum, relu);
+    LAUNCH_OK();
+}

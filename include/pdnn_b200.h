@@ -89,6 +89,15 @@ int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, con
                       const void* residual, void* y, float* mean_invstd, float* running_mean,
                       float* running_var, long long M, int C, float eps, float momentum, int relu,
                       void* stream);
+/* BatchNorm forward for callers that cannot hand us scratch memory (no counterpart in the reference, which
+ * never runs on a device). Same result as pdnn_bn_fwd_stats followed by pdnn_bn_fwd_apply, but the [2][C]
+ * statistics live in a fixed device array inside the library (C <= 2048, 16 KiB per GPU) and are cleared on
+ * every call, so the call performs no allocation of any kind. Calls on one GPU share that array: do not let two
+ * of them overlap. The first call on a device resolves the array's address; issue it before any stream capture.
+ * C above the limit is rejected with an error. Inputs and outputs are passed exactly as for the two-call form. */
+int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const float* beta, const void* residual, void* y,
+                        float* mean_invstd, float* running_mean, float* running_var, long long M, int C,
+                        float eps, float momentum, int relu, void* stream);
 /* sums: [2][C] fp32, zero on entry: sum(dz), sum(dz * xhat), dz = dy * (y > 0 if relu). */
 int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums,
                        long long M, int C, int relu, void* stream);
