@@ -1,0 +1,89 @@
+"""CPU multi-process tests (gloo, world_size 3): BASELINE config 1 -- LeNet on MNIST-shape data, master + 2 workers."""
+import json
+import os
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+pytestmark = pytest.mark.slow
+
+
+def _run(extra, tmp_path, nprocs=3, timeout=240):
+    from pytorch_distributed_nn_b200.parallel.launch import spawn_local
+    args = [os.path.join(ROOT, "distributed_nn.py"), "--network", "LeNet", "--dataset", "MNIST", "--synthetic", "--no-cuda",
+            "--batch-size", "16", "--log-interval", "1", "--train-dir", str(tmp_path)] + extra
+    outs = spawn_local(args, nprocs, timeout=timeout)
+    for rc, o in outs:
+        assert rc == 0, o[-3000:]
+    return outs
+
+
+def _master_log(tmp_path):
+    with open(os.path.join(str(tmp_path), "master_rank0.jsonl")) as f:
+        return [json.loads(l) for l in f if '"step"' in l]
+
+
+def test_all_n_training_equals_single_process_replay(tmp_path):
+    """Master + 2 workers, wait-for-all: the checkpointed weights equal a single-process replay that averages the two
+    workers' gradients (same init seed, same per-worker data streams) -- i.e. the wire protocol loses nothing."""
+    steps, lr, mu = 4, 0.05, 0.5
+    _run(["--max-steps", str(steps), "--straggler-policy", "all", "--lr", str(lr), "--momentum", str(mu), "--eval-freq", "4",
+          "--grad-dtype", "fp32", "--comm-type", "Bcast"], tmp_path)
+    from pytorch_distributed_nn_b200 import mnist
+    from pytorch_distributed_nn_b200.models import build_model
+    from pytorch_distributed_nn_b200.utils import checkpoint as ckpt
+    sd, step, _ = ckpt.load_checkpoint(ckpt.latest_checkpoint(str(tmp_path))[0])
+    assert step == steps
+    torch.manual_seed(1)                                   # --seed default: the master's init
+    net = build_model("LeNet", split=True)
+    data = [mnist.read_data_sets("MNIST_data", reshape=True, synthetic=True, worker_id=r, n_workers=3).train for r in (1, 2)]
+    params = list(net.parameters())
+    mom = [torch.zeros_like(p) for p in params]
+    for _ in range(steps):
+        gsum = [torch.zeros_like(p) for p in params]
+        for d in data:
+            x, y = d.next_batch(16)
+            net.zero_grad()
+            out = net(torch.from_numpy(x).float())
+            loss = torch.nn.functional.cross_entropy(out, torch.from_numpy(y))
+            loss.backward()
+            net.backward(out.grad, None, [])
+            for g, p in zip(gsum, params):
+                g += p.grad
+        with torch.no_grad():
+            for p, g, m in zip(params, gsum, mom):
+                m.mul_(mu).add_(g / 2)
+                p.add_(m, alpha=-lr)
+    for (k, v), p in zip(net.named_parameters(), params):
+        assert torch.allclose(sd[k], p.detach(), rtol=1e-5, atol=1e-6), k
+    log = _master_log(tmp_path)
+    assert [r["selected"] for r in log] == [[0, 1]] * steps and all(r["killed"] == [] for r in log)
+
+
+def test_k_of_n_kills_the_injected_straggler(tmp_path):
+    """k = 1 of 2 with a 400 ms injected delay on rank 2: every step the master selects worker 0, names worker 1 in
+    the kill list, and rank 2 abandons its backward (no host round trip besides the kill message itself)."""
+    outs = _run(["--max-steps", "4", "--num-aggregate", "1", "--inject-delay", "const:ranks=2:ms=400", "--comm-type", "Async"], tmp_path)
+    log = _master_log(tmp_path)
+    assert len(log) == 4
+    # step 1 is dominated by process start-up skew; from step 2 on the injected delay decides
+    assert all(r["selected"] == [0] and r["killed"] == [1] for r in log[1:])
+    with open(os.path.join(str(tmp_path), "worker_rank2.jsonl")) as f:
+        w2 = [json.loads(l) for l in f]
+    assert sum(1 for r in w2 if r["killed"]) >= 2
+    with open(os.path.join(str(tmp_path), "worker_rank1.jsonl")) as f:
+        assert not any(json.loads(l)["killed"] for l in list(f)[1:])
+
+
+def test_evaluator_rank_and_interval_policy(tmp_path):
+    """4 ranks: master, 2 workers, evaluator (C++ reference role). Interval policy: the master closes each step at the
+    deadline with whatever arrived (TF reference's interval mode)."""
+    _run(["--max-steps", "3", "--straggler-policy", "interval", "--interval-ms", "150", "--inject-delay", "const:ranks=2:ms=600",
+          "--evaluator"], tmp_path, nprocs=4)
+    log = _master_log(tmp_path)
+    assert all(r["selected"] == [0] for r in log[1:])
+    rows = open(os.path.join(str(tmp_path), "time_loss_out_SyncReplicas")).read().strip().splitlines()
+    assert len(rows) == 3 and all(len(r.split()) == 4 for r in rows)

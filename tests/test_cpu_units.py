@@ -1,0 +1,185 @@
+"""CPU unit tests: k-of-n oracle, delay models, checkpoints, data readers, layer-split autograd, flags."""
+import argparse
+import os
+
+import numpy as np
+import pytest
+import torch
+
+
+def test_select_first_k_counts_complete_sets_in_arrival_order():
+    from pytorch_distributed_nn_b200.parallel.oracle import select_first_k
+    assert select_first_k([3, 1, 1, 0, 2], 2, 4) == ([1, 3], [0, 2])
+    assert select_first_k([0, 1, 2], 3, 3) == ([0, 1, 2], [])
+    assert select_first_k([2], 1, 3) == ([2], [0, 1])
+
+
+@pytest.mark.parametrize("avg_mode,scale", [("k", 1 / 2), ("n", 1 / 4), ("received", 1 / 2)])
+def test_kofn_update_matches_hand_computation(avg_mode, scale):
+    from pytorch_distributed_nn_b200.parallel.oracle import kofn_update
+    torch.manual_seed(0)
+    w, m = torch.randn(50), torch.randn(50) * 0.1
+    grads = {i: torch.randn(50) for i in range(4)}
+    new_w, new_m, sel, killed = kofn_update(w, m, grads, [2, 0, 3, 1], k=2, n_workers=4, lr=0.1, mu=0.9, avg_mode=avg_mode)
+    assert sel == [0, 2] and killed == [1, 3]
+    g = (grads[0] + grads[2]) * scale
+    assert torch.allclose(new_m, 0.9 * m + g)
+    assert torch.allclose(new_w, w - 0.1 * (0.9 * m + g))
+
+
+def test_momentum_zero_reproduces_reference_plain_sgd():
+    """``--avg-mode=n --momentum 0`` is the python reference's update: param -= lr * sum/n (sync_replicas_master_nn.py:212-219)."""
+    from pytorch_distributed_nn_b200.parallel.oracle import kofn_update
+    from pytorch_distributed_nn_b200.sync_replicas_master_nn import update_params_dist_version
+    w = torch.randn(20)
+    grads = {0: torch.randn(20), 1: torch.randn(20)}
+    new_w, _, _, _ = kofn_update(w, torch.zeros(20), grads, [0, 1], 2, 2, lr=0.01, mu=0.0, avg_mode="n")
+    ref = update_params_dist_version(w.clone(), (grads[0] + grads[1]) / 2, 0.01)
+    assert torch.equal(new_w, ref)
+
+
+def test_delay_specs_are_deterministic_and_respect_rank_subsets():
+    from pytorch_distributed_nn_b200.parallel.delays import parse_delay_spec, summarize_ms
+    f = parse_delay_spec("const:ranks=1,2,3:ms=500:scale=0.01")
+    assert f(0, 1) == f(1, 5) == f(2, 9) == 5_000_000            # workers 0..2 == reference ranks 1..3
+    assert f(3, 1) == 0
+    u = parse_delay_spec("uniform:lo=300:hi=1200:scale=0.001")
+    vals = [u(w, s) for w in range(4) for s in range(50)]
+    assert all(300_000 <= v <= 1_200_000 for v in vals)
+    assert vals == [parse_delay_spec("uniform:lo=300:hi=1200:scale=0.001")(w, s) for w in range(4) for s in range(50)]
+    for spec in ("exp:shift=1:mean=2", "lognormal:mu=0:sigma=1", "pareto:xm=1:alpha=1.5", "exp:mean=1:p=0.25"):
+        g = parse_delay_spec(spec)
+        xs = [g(1, s) / 1e6 for s in range(400)]
+        st = summarize_ms(xs)
+        assert st["p99"] >= st["p50"] >= 0 and st["max"] >= st["p99"]
+    sparse = [parse_delay_spec("exp:mean=1:p=0.25")(0, s) for s in range(400)]
+    assert 0.1 < sum(1 for v in sparse if v > 0) / 400 < 0.4
+
+
+def test_checkpoint_layout_is_a_plain_state_dict(tmp_path):
+    from pytorch_distributed_nn_b200.models import build_model
+    from pytorch_distributed_nn_b200.utils import checkpoint as ckpt
+    net = build_model("LeNet")
+    path, _ = ckpt.save_checkpoint(str(tmp_path), 40, net.state_dict(), momentum=torch.ones(7))
+    assert os.path.basename(path) == "model_step_40"
+    ckpt.save_checkpoint(str(tmp_path), 120, net.state_dict())
+    assert ckpt.latest_checkpoint(str(tmp_path))[1] == 120
+    raw = torch.load(path)                                           # nothing but the model's own keys
+    assert list(raw.keys()) == list(net.state_dict().keys())
+    fresh = build_model("LeNet")
+    fresh.load_state_dict(raw)
+    sd, step, mom = ckpt.load_checkpoint(path)
+    assert step == 40 and torch.equal(mom, torch.ones(7))
+    for k, v in net.state_dict().items():
+        assert torch.equal(sd[k], v)
+
+
+def test_dataset_next_batch_epochs_and_per_worker_shuffle():
+    from pytorch_distributed_nn_b200 import cifar10, mnist
+    from pytorch_distributed_nn_b200.datasets import Cifar10Dataset, MNISTDataset
+    a = mnist.read_data_sets("does-not-exist", reshape=True, worker_id=1)
+    b = mnist.read_data_sets("does-not-exist", reshape=True, worker_id=2)
+    xa, ya = a.train.next_batch(64)
+    xb, yb = b.train.next_batch(64)
+    assert xa.shape == (64, 1, 28, 28) and xa.min() >= -0.5 and xa.max() <= 0.5
+    assert not np.array_equal(ya, yb)                                # workers do not see identical batches (§2.11-6)
+    n = a.train.num_examples
+    for _ in range(n // 64 + 1):
+        a.train.next_batch(64)
+    assert a.train.epochs_completed == 1
+    c = cifar10.read_data_sets(padding_size=2, reshape=True)
+    x, y = Cifar10Dataset(c.train, None).next_batch(8)
+    assert tuple(x.shape) == (8, 3, 32, 32) or tuple(x.shape) == (8, 3, 36, 36)
+    assert x.dtype == torch.float32 and y.dtype == torch.int64 and float(x.max()) > 1.0
+    assert len(MNISTDataset(a.train, None)) == n
+
+
+def test_mnist_idx_reader_parses_big_endian_files(tmp_path):
+    import gzip
+    import struct
+    from pytorch_distributed_nn_b200.utils.data import extract_data, extract_labels
+    imgs = (np.arange(3 * 28 * 28) % 256).astype(np.uint8)
+    with gzip.open(tmp_path / "img.gz", "wb") as f:
+        f.write(struct.pack(">IIII", 2051, 3, 28, 28) + imgs.tobytes())
+    with open(tmp_path / "lab", "wb") as f:
+        f.write(struct.pack(">II", 2049, 3) + bytes([7, 1, 9]))
+    x = extract_data(str(tmp_path / "img.gz"), 3)
+    assert x.shape == (3, 28, 28, 1) and abs(float(x[0, 0, 1, 0]) - (1 - 127.5) / 255) < 1e-6
+    assert extract_labels(str(tmp_path / "lab"), 3).tolist() == [7, 1, 9]
+
+
+@pytest.mark.parametrize("name", ["LeNet", "ResNet18", "VGG11", "MLP"])
+def test_split_backward_equals_autograd_and_streams_in_reverse_order(name):
+    from pytorch_distributed_nn_b200.models import build_model, input_shape
+    torch.manual_seed(0)
+    plain, split = build_model(name), build_model(name, split=True)
+    split.load_state_dict(plain.state_dict())
+    x = torch.randn(4, *input_shape(name))
+    y = torch.randint(0, 10, (4,))
+    torch.nn.functional.cross_entropy(plain(x), y).backward()
+    out = split(x)
+    torch.nn.functional.cross_entropy(out, y).backward()
+    sent = []
+
+    class Comm:
+        def send_grad(self, idx, g):
+            sent.append((idx, g.clone()))
+
+    split.backward(out.grad, Comm(), [])
+    params = list(plain.parameters())
+    assert [i for i, _ in sent] == list(range(len(params) - 1, -1, -1))      # strictly reverse parameters() order
+    assert split.fetch_init_channel_index == len(params)
+    for idx, g in sent:
+        assert torch.allclose(g, params[idx].grad, atol=1e-6)
+
+
+def test_split_backward_signal_kill_stops_sending():
+    from pytorch_distributed_nn_b200.models import build_model
+    split = build_model("LeNet", split=True)
+    out = split(torch.randn(2, 1, 28, 28))
+    out.sum().backward()
+    sent = []
+
+    class Comm:
+        calls = 0
+
+        def send_grad(self, idx, g):
+            sent.append(idx)
+
+        def should_abort(self, step):
+            Comm.calls += 1
+            return Comm.calls > 3          # killed before the 4th op of the reversed walk
+
+    reqs, killed = split.backward_signal_kill(out.grad, Comm(), [], cur_step=5)
+    assert killed and sent == [7, 6, 5, 4]      # fc2 (bias, weight), fc1 (bias, weight); conv grads never leave
+
+
+def test_accuracy_and_flags():
+    from pytorch_distributed_nn_b200.nn_ops import accuracy
+    from pytorch_distributed_nn_b200.utils.config import add_fit_args, kwargs_from_args
+    out = torch.tensor([[0.1, 0.9, 0.0], [0.8, 0.1, 0.1], [0.2, 0.3, 0.5]])
+    p1, p2 = accuracy(out, torch.tensor([1, 2, 2]), topk=(1, 2))
+    assert abs(float(p1) - 200 / 3) < 1e-4 and abs(float(p2) - 200 / 3) < 1e-4
+    args = add_fit_args(argparse.ArgumentParser()).parse_args([])
+    assert (args.batch_size, args.test_batch_size, args.epochs, args.lr, args.momentum, args.seed, args.log_interval) == \
+        (128, 1000, 100, 0.01, 0.5, 1, 10)
+    assert (args.network, args.dataset, args.comm_type, args.num_aggregate, args.no_cuda) == ("LeNet", "MNIST", "Bcast", 5, False)
+    kw = kwargs_from_args(args, master=True)
+    for key in ("batch_size", "learning_rate", "max_epochs", "momentum", "network", "comm_method", "kill_threshold"):
+        assert key in kw
+    assert "kill_threshold" not in kwargs_from_args(args, master=False)
+
+
+def test_engine_layout_matches_torch_parameter_order_on_meta_device():
+    from pytorch_distributed_nn_b200.engine.network import build_network
+    from pytorch_distributed_nn_b200.models import build_model
+    for name, count in (("LeNet", 8), ("ResNet18", 62), ("ResNet50", 161), ("VGG11", 34)):
+        net = build_network(name, 128, device="meta")
+        ref = build_model(name)
+        assert [p.name for p in net.param_list] == [k for k, _ in ref.named_parameters()]
+        assert [p.torch_shape for p in net.param_list] == [tuple(v.shape) for v in ref.parameters()]
+        assert len(net.param_list) == count
+        spans = sorted((b.start, b.end) for b in net.buckets)
+        assert spans[0][0] == 0 and spans[-1][1] == net.total
+        assert all(spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1))
+        assert net.buckets[0].end == net.total                      # bucket 0 = deepest layers, closes first
