@@ -45,7 +45,7 @@ class B200ParameterServer:
                  momentum: float = 0.0, num_aggregate: Optional[int] = None, avg_mode: str = "k",
                  grad_dtype: str = "bf16", colocate: bool = True, n_buckets: int = 8, seed: int = 0,
                  deadline_ms: float = 0.0, delay_fn: Optional[Callable[[int, int], int]] = None, group=None,
-                 device=None):
+                 device=None, init_state_dict=None):
         assert torch.cuda.is_available(), "the b200 backend needs a GPU (use --backend gloo on CPU)"
         self.rank, self.world = rank, world_size
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -69,6 +69,8 @@ class B200ParameterServer:
         net = self.net
         if self.is_master:
             net.init_parameters(seed)          # fills w32 and (through sync_compute_weights) the local w
+            if init_state_dict is not None:    # resume: the checkpoint replaces the random init before the first broadcast
+                net.load_state_dict(init_state_dict)
             self.momentum = torch.zeros(net.total, device=self.device, dtype=torch.float32)
         self._install_hooks()
         self._initial_broadcast(group)

@@ -130,17 +130,17 @@ class SyncReplicasMaster_NN(NN_Trainer):
         from .parallel.b200_ps import B200ParameterServer
         from .parallel.delays import parse_delay_spec
         delay_fn = parse_delay_spec(self.inject_delay) if self.inject_delay else None
+        init_sd, self.step_offset = None, 0
+        if self.resume:
+            # the device protocol always counts from 1; the global step (checkpoint names) continues from the file
+            init_sd, self.step_offset, _ = ckpt.load_checkpoint(self.resume)
         self.ps = B200ParameterServer(self.network_config, self.batch_size, self.comm.Get_rank(), self.world_size, lr=self.lr,
                                       momentum=self.momentum, num_aggregate=self._should_kill_threshold, avg_mode=self.avg_mode,
                                       grad_dtype="bf16" if self.grad_dtype == "bf16" else "fp32", colocate=self.colocate or self.world_size == 1,
                                       n_buckets=self.n_buckets, seed=self.seed,
                                       deadline_ms=self.interval_ms if self.policy == "interval" else 0.0, delay_fn=delay_fn,
-                                      group=self.comm.group, device=self.comm.device)
+                                      group=self.comm.group, device=self.comm.device, init_state_dict=init_sd)
         self.network = self.ps.net
-        if self.resume:
-            sd, step, mom = ckpt.load_checkpoint(self.resume)
-            self.ps.net.load_state_dict(sd)
-            self.ps.rebroadcast()
         return self
 
     def init_model_shapes(self):
@@ -238,7 +238,7 @@ class SyncReplicasMaster_NN(NN_Trainer):
                 print("Master Step: {} selected: {} killed: {} Step Time: {:.6f}".format(i, selected, killed, ms / 1e3), flush=True)
                 self.logger.log(step=i, selected=selected, killed=killed, step_ms=ms)
                 if self.eval_freq and self.train_dir and i % self.eval_freq == 0:
-                    self.cur_step = i
+                    self.cur_step = i + getattr(self, "step_offset", 0)
                     self.save_checkpoint()
         torch.cuda.synchronize()
         self.cur_step = ps.step
