@@ -1,0 +1,506 @@
+// Native (C++/CUDA) fully-connected parameter server: master / worker / evaluator roles without Python in the loop.
+//
+// Counterpart of the reference's only native component, MPI_code/ (C++11 + MPI + cblas_dgemm):
+//   NNParams            nn_params.h:16-76          -> fcps::NNParams (layer list, batch, lr, dimension validation)
+//   NNLayer / NN        nn_layer.h, nn.h           -> fcps::Net (bias folded in as the last weight row, sigmoid hidden
+//                                                    layers, softmax cross-entropy output, loss / error rate)
+//   SyncReplicasMasterNN sync_replicas_master_nn.h -> fcps::master_loop ((layer, step)-addressed slots, arrival-order
+//                                                    accumulation, stale contributions dropped by step tag, per-layer
+//                                                    mean over what arrived, n_to_collect threshold)
+//   WorkerNN            worker_nn.h                -> fcps::worker_loop (just-in-time per-layer weight fetch, per-layer
+//                                                    gradient push during backward, SHORTCIRCUIT: abandon the step the
+//                                                    moment a newer step is published)
+//   EvaluatorNN         evaluator_nn.h             -> fcps::evaluator_loop (outfiles/time_loss_out_<scheme>)
+//   mnist.h             IDX reader, /255, shuffle  -> fcps::load_mnist (+ synthetic fallback, loader self-test)
+//
+// B200 design: roles are host threads of ONE process, each bound to a GPU (all on one GPU when only one exists);
+// weights, slots and activations live in device memory; transfers between roles are device-to-device copies on the
+// sender's stream (NVLink peer copies across GPUs); the math runs on this library's kernels. Step tags live in host
+// atomics -- kernels never spin on one another, so the protocol is safe with any number of roles per GPU.
+#include "common.cuh"
+#include "../include/pdnn_b200.h"
+
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <fstream>
+#include <mutex>
+#include <random>
+#include <string>
+#include <thread>
+#include <vector>
+#include <string.h>
+#include <sys/stat.h>
+
+namespace fcps {
+
+#define FC_CUDA(expr)                                                                               \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess) {                                                                    \
+            fprintf(stderr, "fc_ps: %s:%d %s -> %s\n", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            failed.store(true);                                                                     \
+            return;                                                                                 \
+        }                                                                                           \
+    } while (0)
+
+static double now_ms() {
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+__global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float alpha, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) y[i] += alpha * x[i];
+}
+__global__ void apply_grad_kernel(const float* __restrict__ w_old, const float* __restrict__ acc, float* __restrict__ w_new, float alpha, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        w_new[i] = w_old[i] - alpha * acc[i];
+}
+__global__ void error_count_kernel(const float* __restrict__ logits, const long long* __restrict__ labels, int B, int C, int* wrong) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < B; r += gridDim.x * blockDim.x) {
+        int best = 0;
+        for (int c = 1; c < C; ++c) if (logits[(long long)r * C + c] > logits[(long long)r * C + best]) best = c;
+        if (best != (int)labels[r]) atomicAdd(wrong, 1);
+    }
+}
+
+struct NNParams {
+    std::vector<int> dims;
+    int batch = 128;
+    float lr = 1e-3f;
+    bool validate(std::string* why) const {
+        if (dims.size() < 2) { *why = "need at least an input and an output dimension"; return false; }
+        for (int d : dims) if (d <= 0) { *why = "non-positive layer dimension"; return false; }
+        if (batch <= 0) { *why = "non-positive batch size"; return false; }
+        return true;
+    }
+    int n_layers() const { return (int)dims.size() - 1; }
+    long long layer_elems(int l) const { return (long long)(dims[l] + 1) * dims[l + 1]; }   // bias folded in as last row
+};
+
+struct Dataset {
+    std::vector<float> images;       // [n][784] scaled to [0,1]
+    std::vector<long long> labels;
+    int n = 0, dim = 784;
+};
+
+// big-endian IDX files (reference mnist.h:25-86); /255 scaling (:102-109); Fisher-Yates shuffle (:132-138)
+static bool read_idx(const std::string& img, const std::string& lab, Dataset* d) {
+    std::ifstream fi(img, std::ios::binary), fl(lab, std::ios::binary);
+    if (!fi || !fl) return false;
+    auto be32 = [](std::ifstream& f) { unsigned char b[4]; f.read((char*)b, 4); return (int)((b[0] << 24) | (b[1] << 16) | (b[2] << 8) | b[3]); };
+    if (be32(fi) != 2051) return false;
+    int n = be32(fi), r = be32(fi), c = be32(fi);
+    if (be32(fl) != 2049 || be32(fl) != n) return false;
+    d->n = n; d->dim = r * c;
+    std::vector<unsigned char> raw((size_t)n * r * c), lraw(n);
+    fi.read((char*)raw.data(), raw.size());
+    fl.read((char*)lraw.data(), n);
+    d->images.resize(raw.size());
+    for (size_t i = 0; i < raw.size(); ++i) d->images[i] = raw[i] / 255.f;
+    d->labels.assign(lraw.begin(), lraw.end());
+    return true;
+}
+static void synthetic(Dataset* d, int n, int dim, int classes, unsigned seed) {
+    std::mt19937 rng(seed);
+    std::uniform_real_distribution<float> u(0.f, 1.f);
+    std::normal_distribution<float> g(0.f, 1.f);
+    std::vector<float> proj((size_t)dim * classes);
+    std::mt19937 prng(12345);
+    for (auto& p : proj) p = g(prng);
+    d->n = n; d->dim = dim;
+    d->images.resize((size_t)n * dim);
+    d->labels.resize(n);
+    for (int i = 0; i < n; ++i) {
+        float mean = 0.f;
+        for (int j = 0; j < dim; ++j) { d->images[(size_t)i * dim + j] = u(rng); mean += d->images[(size_t)i * dim + j]; }
+        mean /= dim;
+        int best = 0; float bv = -1e30f;
+        for (int c = 0; c < classes; ++c) {
+            float s = 0.f;
+            for (int j = 0; j < dim; ++j) s += (d->images[(size_t)i * dim + j] - mean) * proj[(size_t)j * classes + c];
+            if (s > bv) { bv = s; best = c; }
+        }
+        d->labels[i] = best;
+    }
+}
+static void shuffle(Dataset* d, unsigned seed) {
+    std::mt19937 rng(seed);
+    for (int i = d->n - 1; i > 0; --i) {
+        int j = (int)(rng() % (unsigned)(i + 1));
+        if (i == j) continue;
+        for (int k = 0; k < d->dim; ++k) std::swap(d->images[(size_t)i * d->dim + k], d->images[(size_t)j * d->dim + k]);
+        std::swap(d->labels[i], d->labels[j]);
+    }
+}
+static bool load_mnist(const char* dir, Dataset* d, int synth_n, int dim, int classes, unsigned seed) {
+    if (dir != nullptr && dir[0]) {
+        std::string b(dir);
+        if (read_idx(b + "/train-images-idx3-ubyte", b + "/train-labels-idx1-ubyte", d)) { shuffle(d, seed); return true; }
+    }
+    synthetic(d, synth_n, dim, classes, seed);
+    return false;
+}
+
+// A network instance of one role: device buffers on that role's GPU.
+struct Net {
+    NNParams p;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<float*> W, G, Z, D;   // per layer: weights, gradient, activation output, delta
+    float* X = nullptr;               // input batch
+    long long* Y = nullptr;
+    float* loss = nullptr;
+    int* wrong = nullptr;
+    std::atomic<bool>& failed;
+    Net(const NNParams& prm, int dev, std::atomic<bool>& f) : p(prm), device(dev), failed(f) {}
+    void init() {
+        FC_CUDA(cudaSetDevice(device));
+        FC_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+        const int L = p.n_layers();
+        W.resize(L); G.resize(L); Z.resize(L); D.resize(L);
+        for (int l = 0; l < L; ++l) {
+            FC_CUDA(cudaMalloc(&W[l], sizeof(float) * p.layer_elems(l)));
+            FC_CUDA(cudaMalloc(&G[l], sizeof(float) * p.layer_elems(l)));
+            FC_CUDA(cudaMalloc(&Z[l], sizeof(float) * (size_t)p.batch * p.dims[l + 1]));
+            FC_CUDA(cudaMalloc(&D[l], sizeof(float) * (size_t)p.batch * p.dims[l + 1]));
+        }
+        FC_CUDA(cudaMalloc(&X, sizeof(float) * (size_t)p.batch * p.dims[0]));
+        FC_CUDA(cudaMalloc(&Y, sizeof(long long) * p.batch));
+        FC_CUDA(cudaMalloc(&loss, sizeof(float)));
+        FC_CUDA(cudaMalloc(&wrong, sizeof(int)));
+    }
+    void destroy() {
+        cudaSetDevice(device);
+        for (auto v : {&W, &G, &Z, &D}) for (float* q : *v) cudaFree(q);
+        cudaFree(X); cudaFree(Y); cudaFree(loss); cudaFree(wrong);
+        if (stream) cudaStreamDestroy(stream);
+    }
+    void fill_batch(const Dataset& d, int* cursor) {
+        if (*cursor + p.batch > d.n) *cursor = 0;
+        FC_CUDA(cudaMemcpyAsync(X, d.images.data() + (size_t)*cursor * d.dim, sizeof(float) * (size_t)p.batch * d.dim, cudaMemcpyHostToDevice, stream));
+        FC_CUDA(cudaMemcpyAsync(Y, d.labels.data() + *cursor, sizeof(long long) * p.batch, cudaMemcpyHostToDevice, stream));
+        *cursor += p.batch;
+    }
+    // S = [Z|1] W ; Z = sigmoid(S) on hidden layers (reference nn_layer.h:97-142)
+    bool forward_layer(int l) {
+        const int L = p.n_layers();
+        const float* in = l == 0 ? X : Z[l - 1];
+        const int n_in = p.dims[l], n_out = p.dims[l + 1];
+        if (pdnn_gemm_simt_f32(in, 0, n_in, W[l], 0, n_out, Z[l], n_out, p.batch, n_out, n_in, 1.f, W[l] + (size_t)n_in * n_out, 0, 0, stream)) return false;
+        if (l < L - 1 && pdnn_sigmoid_fwd_f32(Z[l], Z[l], (long long)p.batch * n_out, stream)) return false;
+        return true;
+    }
+    bool output_delta() {   // softmax + cross-entropy: D = (softmax - onehot) / B, loss = mean CE
+        const int L = p.n_layers();
+        cudaMemsetAsync(loss, 0, sizeof(float), stream);
+        return pdnn_cross_entropy_fwd_bwd_f32(Z[L - 1], Y, loss, D[L - 1], nullptr, p.batch, p.dims[L], p.dims[L], stream) == 0;
+    }
+    // grad = [Z|1]^T D ; D_prev = (D W^T) o sigmoid'  (reference nn_layer.h:144-178)
+    bool backward_layer(int l) {
+        const float* in = l == 0 ? X : Z[l - 1];
+        const int n_in = p.dims[l], n_out = p.dims[l + 1];
+        cudaMemsetAsync(G[l], 0, sizeof(float) * p.layer_elems(l), stream);
+        if (pdnn_gemm_simt_f32(in, 1, n_in, D[l], 0, n_out, G[l], n_out, n_in, n_out, p.batch, 1.f, nullptr, 0, 1, stream)) return false;
+        if (pdnn_col_sum_f32(D[l], n_out, G[l] + (size_t)n_in * n_out, p.batch, n_out, 1, stream)) return false;
+        if (l > 0) {
+            if (pdnn_gemm_simt_f32(D[l], 0, n_out, W[l], 1, n_out, D[l - 1], n_in, p.batch, n_in, n_out, 1.f, nullptr, 0, 0, stream)) return false;
+            if (pdnn_sigmoid_bwd_f32(Z[l - 1], D[l - 1], D[l - 1], (long long)p.batch * n_in, stream)) return false;
+        }
+        return true;
+    }
+};
+
+struct Arrival { int worker, layer, step; };
+
+struct Board {
+    NNParams p;
+    pdnn_fc_ps_config_t cfg;
+    int n_workers = 0;
+    std::atomic<int> cur_step{0};
+    std::atomic<bool> failed{false};
+    std::mutex mu;
+    std::condition_variable cv_step, cv_arrival;
+    std::deque<Arrival> arrivals;
+    // master-side device memory (device 0): weights double-buffered by step parity, one slot per (worker, layer)
+    std::vector<float*> Wm[2];
+    std::vector<std::vector<float*>> slots;
+    std::vector<float*> acc;
+    int master_device = 0;
+    // statistics
+    std::vector<double> step_ms;
+    long long accepted = 0, dropped_stale = 0, abandoned_steps = 0;
+    std::vector<float> eval_loss, eval_err;
+    std::vector<double> timeline_ms;
+    std::vector<int> timeline_step, timeline_who;
+    std::string scheme;
+};
+
+static void copy_d2d(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes, cudaStream_t s) {
+    if (dst_dev == src_dev) cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, s);
+    else cudaMemcpyPeerAsync(dst, dst_dev, src, src_dev, bytes, s);
+}
+
+static void worker_loop(Board* b, int w, int device, const Dataset* data) {
+    std::atomic<bool>& failed = b->failed;
+    Net net(b->p, device, failed);
+    net.init();
+    if (failed.load()) return;
+    const int L = b->p.n_layers();
+    int my_step = 0, cursor = (w * 997 * b->p.batch) % std::max(1, data->n - b->p.batch);
+    const long long delay_us = (b->cfg.delay_worker_mask >> w) & 1 ? b->cfg.delay_us_per_layer : 0;
+    auto step_changed = [&]() { return b->cfg.shortcircuit && b->cur_step.load(std::memory_order_acquire) != my_step; };
+    while (!failed.load()) {
+        {
+            std::unique_lock<std::mutex> lk(b->mu);
+            b->cv_step.wait(lk, [&] { return b->cur_step.load() != my_step || failed.load(); });
+            my_step = b->cur_step.load();
+        }
+        if (my_step > b->cfg.n_train_iters || my_step < 0) break;
+        const int par = my_step & 1;
+        net.fill_batch(*data, &cursor);
+        bool abandoned = false;
+        for (int l = 0; l < L && !abandoned; ++l) {
+            if (step_changed()) { abandoned = true; break; }
+            // just-in-time fetch of layer l's weights, overlapped with the previous layer's compute (worker_nn.h:56-74)
+            copy_d2d(net.W[l], device, b->Wm[par][l], b->master_device, sizeof(float) * b->p.layer_elems(l), net.stream);
+            if (!net.forward_layer(l)) { failed.store(true); break; }
+        }
+        if (!abandoned && !net.output_delta()) failed.store(true);
+        for (int l = L - 1; l >= 0 && !abandoned && !failed.load(); --l) {
+            if (delay_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(delay_us));   // injected straggler (pure_py worker:130-132)
+            if (step_changed()) { abandoned = true; break; }
+            if (!net.backward_layer(l)) { failed.store(true); break; }
+            // push this layer's gradient into my slot on the master and announce it, tagged with the step
+            copy_d2d(b->slots[w][l], b->master_device, net.G[l], device, sizeof(float) * b->p.layer_elems(l), net.stream);
+            cudaStreamSynchronize(net.stream);
+            {
+                std::lock_guard<std::mutex> lk(b->mu);
+                b->arrivals.push_back({w, l, my_step});
+            }
+            b->cv_arrival.notify_one();
+        }
+        cudaStreamSynchronize(net.stream);
+        if (abandoned) { std::lock_guard<std::mutex> lk(b->mu); b->abandoned_steps++; }
+    }
+    net.destroy();
+}
+
+static void evaluator_loop(Board* b, int device, const Dataset* data) {
+    std::atomic<bool>& failed = b->failed;
+    Net net(b->p, device, failed);
+    net.init();
+    if (failed.load()) return;
+    const int L = b->p.n_layers();
+    int my_step = 0;
+    const double t0 = now_ms();
+    mkdir("outfiles", 0755);
+    std::string path = std::string(b->cfg.out_dir[0] ? b->cfg.out_dir : "outfiles") + "/time_loss_out_" + b->scheme;
+    mkdir(b->cfg.out_dir[0] ? b->cfg.out_dir : "outfiles", 0755);
+    FILE* f = fopen(path.c_str(), "w");
+    while (!failed.load()) {
+        {
+            std::unique_lock<std::mutex> lk(b->mu);
+            b->cv_step.wait(lk, [&] { return b->cur_step.load() != my_step || failed.load(); });
+            my_step = b->cur_step.load();
+        }
+        if (my_step < 0) break;
+        const int par = my_step & 1;
+        for (int l = 0; l < L; ++l)
+            copy_d2d(net.W[l], device, b->Wm[par][l], b->master_device, sizeof(float) * b->p.layer_elems(l), net.stream);
+        float loss_sum = 0.f; int wrong_sum = 0, seen = 0, cursor = 0;
+        for (int it = 0; it < b->cfg.eval_batches && cursor + b->p.batch <= data->n; ++it) {
+            net.fill_batch(*data, &cursor);
+            for (int l = 0; l < L; ++l) net.forward_layer(l);
+            net.output_delta();
+            cudaMemsetAsync(net.wrong, 0, sizeof(int), net.stream);
+            error_count_kernel<<<4, 128, 0, net.stream>>>(net.Z[L - 1], net.Y, b->p.batch, b->p.dims[L], net.wrong);
+            float hl; int hw;
+            cudaMemcpyAsync(&hl, net.loss, sizeof(float), cudaMemcpyDeviceToHost, net.stream);
+            cudaMemcpyAsync(&hw, net.wrong, sizeof(int), cudaMemcpyDeviceToHost, net.stream);
+            cudaStreamSynchronize(net.stream);
+            loss_sum += hl; wrong_sum += hw; seen += b->p.batch;
+        }
+        const float loss = loss_sum / std::max(1, b->cfg.eval_batches), err = (float)wrong_sum / std::max(1, seen);
+        {
+            std::lock_guard<std::mutex> lk(b->mu);
+            b->eval_loss.push_back(loss);
+            b->eval_err.push_back(err);
+        }
+        if (f) { fprintf(f, "%d %.3f %.6f %.6f\n", my_step, now_ms() - t0, loss, err); fflush(f); }   // step time loss err (evaluator_nn.h:58)
+        if (my_step > b->cfg.n_train_iters) break;
+    }
+    if (f) fclose(f);
+    net.destroy();
+}
+
+static void master_loop(Board* b) {
+    std::atomic<bool>& failed = b->failed;
+    const int L = b->p.n_layers();
+    FC_CUDA(cudaSetDevice(b->master_device));
+    cudaStream_t stream;
+    FC_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    const int n_collect = b->cfg.n_to_collect;
+    std::vector<int> count(L);
+    std::vector<std::vector<char>> seen(b->n_workers, std::vector<char>(L, 0));
+    const double t_begin = now_ms();
+    for (int step = 1; step <= b->cfg.n_train_iters && !failed.load(); ++step) {
+        const double t0 = now_ms();
+        const int par = step & 1;
+        std::fill(count.begin(), count.end(), 0);
+        for (auto& s : seen) std::fill(s.begin(), s.end(), 0);
+        for (int l = 0; l < L; ++l) cudaMemsetAsync(b->acc[l], 0, sizeof(float) * b->p.layer_elems(l), stream);
+        {
+            std::lock_guard<std::mutex> lk(b->mu);
+            b->cur_step.store(step, std::memory_order_release);      // the step message + weights "broadcast" (weights are already in Wm[par])
+            if (b->cfg.generate_timeline) { b->timeline_ms.push_back(now_ms() - t_begin); b->timeline_step.push_back(step); b->timeline_who.push_back(-1); }
+        }
+        b->cv_step.notify_all();
+        bool enough = false;
+        while (!enough && !failed.load()) {
+            Arrival a;
+            {
+                std::unique_lock<std::mutex> lk(b->mu);
+                b->cv_arrival.wait(lk, [&] { return !b->arrivals.empty() || failed.load(); });
+                if (failed.load()) break;
+                a = b->arrivals.front();
+                b->arrivals.pop_front();
+                if (a.step != step) { b->dropped_stale++; continue; }            // stale: tag != cur_step (master.h:85)
+                b->accepted++;
+                if (b->cfg.generate_timeline) { b->timeline_ms.push_back(now_ms() - t_begin); b->timeline_step.push_back(step); b->timeline_who.push_back(a.worker); }
+            }
+            if (seen[a.worker][a.layer]) continue;
+            seen[a.worker][a.layer] = 1;
+            const long long n = b->p.layer_elems(a.layer);
+            axpy_kernel<<<(int)std::min<long long>((n + 255) / 256, 592), 256, 0, stream>>>(b->acc[a.layer], b->slots[a.worker][a.layer], 1.f, n);
+            count[a.layer]++;
+            enough = true;
+            for (int l = 0; l < L; ++l) enough = enough && count[l] >= n_collect;
+        }
+        // apply lr / gradients_accumulated[layer]: mean over what actually arrived, per layer (master.h:124-128)
+        for (int l = 0; l < L; ++l) {
+            const long long n = b->p.layer_elems(l);
+            apply_grad_kernel<<<(int)std::min<long long>((n + 255) / 256, 592), 256, 0, stream>>>(b->Wm[par][l], b->acc[l], b->Wm[par ^ 1][l],
+                                                                                                b->p.lr / (float)std::max(1, count[l]), n);
+        }
+        FC_CUDA(cudaStreamSynchronize(stream));
+        b->step_ms.push_back(now_ms() - t0);
+    }
+    {
+        std::lock_guard<std::mutex> lk(b->mu);
+        b->cur_step.store(b->cfg.n_train_iters + 1, std::memory_order_release);   // the last step message ends workers and evaluator
+    }
+    b->cv_step.notify_all();
+    cudaStreamDestroy(stream);
+}
+
+}  // namespace fcps
+
+extern "C" int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* res) {
+    using namespace fcps;
+    PDNN_REQUIRE(cfg != nullptr && res != nullptr, "fc_ps: null arguments");
+    Board board;
+    Board* b = &board;
+    b->cfg = *cfg;
+    for (int i = 0; i < cfg->n_dims; ++i) b->p.dims.push_back(cfg->dims[i]);
+    b->p.batch = cfg->batch;
+    b->p.lr = cfg->lr;
+    std::string why;
+    PDNN_REQUIRE(b->p.validate(&why), "fc_ps: invalid NNParams: %s", why.c_str());
+    PDNN_REQUIRE(cfg->n_workers >= 1 && cfg->n_workers <= 32, "fc_ps: n_workers out of range");
+    PDNN_REQUIRE(cfg->n_to_collect >= 1 && cfg->n_to_collect <= cfg->n_workers, "fc_ps: n_to_collect must be in [1, n_workers]");
+    b->n_workers = cfg->n_workers;
+    int n_dev = 0;
+    PDNN_CUDA_CHECK(cudaGetDeviceCount(&n_dev));
+    PDNN_REQUIRE(n_dev >= 1, "fc_ps: no CUDA device");
+    if (cfg->max_devices > 0 && n_dev > cfg->max_devices) n_dev = cfg->max_devices;
+    char scheme[128];
+    snprintf(scheme, sizeof(scheme), "SyncReplicasWithBackup%d_%d%s", cfg->n_to_collect, cfg->n_workers, cfg->shortcircuit ? "_shortcircuit" : "");
+    b->scheme = scheme;      // reference scheme_full_name(), distributed_defines.h:30-41
+    // peer access between the GPUs in use
+    for (int i = 0; i < n_dev; ++i)
+        for (int j = 0; j < n_dev; ++j)
+            if (i != j) { cudaSetDevice(i); int can = 0; cudaDeviceCanAccessPeer(&can, i, j); if (can) { cudaDeviceEnablePeerAccess(j, 0); cudaGetLastError(); } }
+    const int L = b->p.n_layers();
+    PDNN_CUDA_CHECK(cudaSetDevice(0));
+    std::mt19937 rng(cfg->seed);
+    b->slots.assign(cfg->n_workers, std::vector<float*>(L, nullptr));
+    for (int par = 0; par < 2; ++par) b->Wm[par].assign(L, nullptr);
+    b->acc.assign(L, nullptr);
+    for (int l = 0; l < L; ++l) {
+        const long long n = b->p.layer_elems(l);
+        for (int par = 0; par < 2; ++par) PDNN_CUDA_CHECK(cudaMalloc(&b->Wm[par][l], sizeof(float) * n));
+        PDNN_CUDA_CHECK(cudaMalloc(&b->acc[l], sizeof(float) * n));
+        for (int w = 0; w < cfg->n_workers; ++w) PDNN_CUDA_CHECK(cudaMalloc(&b->slots[w][l], sizeof(float) * n));
+        // W ~ N(0, 0.1^2), bias row = 0 (pure_py_code/nn/nn_layer.py:58-110)
+        std::vector<float> h(n, 0.f);
+        std::normal_distribution<float> g(0.f, 0.1f);
+        for (long long i = 0; i < (long long)b->p.dims[l] * b->p.dims[l + 1]; ++i) h[i] = g(rng);
+        PDNN_CUDA_CHECK(cudaMemcpy(b->Wm[1][l], h.data(), sizeof(float) * n, cudaMemcpyHostToDevice));   // step 1 reads parity 1
+    }
+    Dataset train, test;
+    const bool real = load_mnist(cfg->data_dir, &train, cfg->synthetic_examples > 0 ? cfg->synthetic_examples : 4096, b->p.dims[0], b->p.dims.back(), cfg->seed);
+    if (real) { test = train; test.n = std::min(train.n, 2048); }
+    else synthetic(&test, 1024, b->p.dims[0], b->p.dims.back(), cfg->seed + 99);
+    PDNN_REQUIRE(train.dim == b->p.dims[0], "fc_ps: dataset dimension %d does not match the input layer %d", train.dim, b->p.dims[0]);
+    PDNN_REQUIRE(train.n >= b->p.batch, "fc_ps: dataset smaller than one batch");
+
+    const double t0 = now_ms();
+    std::vector<std::thread> threads;
+    for (int w = 0; w < cfg->n_workers; ++w) threads.emplace_back(worker_loop, b, w, n_dev > 1 ? 1 + w % (n_dev - 1) : 0, &train);
+    if (cfg->with_evaluator) threads.emplace_back(evaluator_loop, b, n_dev > 1 ? n_dev - 1 : 0, &test);
+    std::thread master(master_loop, b);
+    master.join();
+    for (auto& t : threads) t.join();
+    const double total = now_ms() - t0;
+
+    memset(res, 0, sizeof(*res));
+    res->steps = (int)b->step_ms.size();
+    res->total_ms = total;
+    double sum = 0;
+    for (double v : b->step_ms) sum += v;
+    res->mean_step_ms = b->step_ms.empty() ? 0 : sum / b->step_ms.size();
+    res->gradients_accepted = b->accepted;
+    res->gradients_dropped_stale = b->dropped_stale;
+    res->steps_abandoned = b->abandoned_steps;
+    res->avg_gradients_per_step = b->step_ms.empty() ? 0 : (double)b->accepted / (double)b->step_ms.size() / L;
+    if (!b->eval_loss.empty()) {
+        res->first_loss = b->eval_loss.front(); res->final_loss = b->eval_loss.back();
+        res->first_err = b->eval_err.front(); res->final_err = b->eval_err.back();
+    }
+    snprintf(res->scheme, sizeof(res->scheme), "%s", scheme);
+    if (cfg->generate_timeline) {
+        std::string path = std::string(cfg->out_dir[0] ? cfg->out_dir : "outfiles") + "/timeline_out_" + scheme;
+        mkdir(cfg->out_dir[0] ? cfg->out_dir : "outfiles", 0755);
+        if (FILE* f = fopen(path.c_str(), "w")) {
+            for (size_t i = 0; i < b->timeline_ms.size(); ++i) fprintf(f, "%.3f %d %d\n", b->timeline_ms[i], b->timeline_step[i], b->timeline_who[i] < 0 ? 1 : 0);
+            fclose(f);
+        }
+    }
+    cudaSetDevice(0);
+    for (int l = 0; l < L; ++l) {
+        for (int par = 0; par < 2; ++par) cudaFree(b->Wm[par][l]);
+        cudaFree(b->acc[l]);
+        for (int w = 0; w < cfg->n_workers; ++w) cudaFree(b->slots[w][l]);
+    }
+    PDNN_REQUIRE(!b->failed.load(), "fc_ps: a role failed (see stderr)");
+    return 0;
+}
+
+// Loader / network self-tests of the reference (mnist.h:155-162 test_load_data, nn.h:158-207 test_nn):
+// returns 0 when a 784-100-10 net trained for `iters` single-worker steps reduces its loss.
+extern "C" int pdnn_fc_ps_selftest(int iters, float* first_loss, float* last_loss) {
+    pdnn_fc_ps_config_t c;
+    memset(&c, 0, sizeof(c));
+    c.n_dims = 3; c.dims[0] = 784; c.dims[1] = 100; c.dims[2] = 10;
+    c.batch = 128; c.lr = 0.5f; c.n_workers = 1; c.n_to_collect = 1; c.n_train_iters = iters; c.with_evaluator = 1; c.eval_batches = 2;
+    c.seed = 7; c.synthetic_examples = 2048; c.max_devices = 1;
+    snprintf(c.out_dir, sizeof(c.out_dir), "/tmp/pdnn_fc_selftest");
+    pdnn_fc_ps_result_t r;
+    if (int rc = pdnn_fc_ps_run(&c, &r)) return rc;
+    if (first_loss) *first_loss = r.first_loss;
+    if (last_loss) *last_loss = r.final_loss;
+    PDNN_REQUIRE(r.final_loss < r.first_loss, "fc_ps selftest: loss did not decrease (%f -> %f)", r.first_loss, r.final_loss);
+    return 0;
+}

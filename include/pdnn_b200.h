@@ -206,6 +206,63 @@ int pdnn_enable_peer_access(int peer_device);
 /* Link microbenchmarks: copy n bytes local->dst (peer) with 16-byte stores. */
 int pdnn_p2p_copy(const void* src, void* dst, long long nbytes, int max_ctas, void* stream);
 
+/* fp32 variants used by the small-shape (LeNet / FC-MLP) path; same semantics as the bf16 entry points above. */
+int pdnn_nchw_f32_to_nhwc_f32(const float* x, float* y, int N, int C, int H, int W, int Cpad, void* stream);
+int pdnn_im2col_f32(const float* x, float* col, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH, int OW,
+                    int Kpad, void* stream);
+int pdnn_col2im_f32(const float* dcol, float* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH, int OW,
+                    int Kpad, void* stream);
+int pdnn_relu_fwd_f32(const float* x, float* y, long long n, void* stream);
+int pdnn_relu_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream);
+int pdnn_maxpool2_fwd_f32(const float* x, float* y, int N, int H, int W, int C, void* stream);
+int pdnn_maxpool2_bwd_f32(const float* x, const float* y, const float* dy, float* dx, int N, int H, int W, int C, void* stream);
+int pdnn_col_sum_f32(const float* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream);
+int pdnn_cross_entropy_fwd_bwd_f32(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
+                                   int B, int classes, int ld, void* stream);
+int pdnn_sigmoid_fwd_f32(const float* x, float* y, long long n, void* stream);
+int pdnn_sigmoid_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream);
+
+/* raw device allocations for peer-mapped communication arenas (zero-filled) */
+int pdnn_malloc(void** out, long long nbytes);
+int pdnn_free(void* p);
+
+/* ---------------------------------------------------------------------------------------------
+ * Native fully-connected parameter server (csrc/fc_ps_native.cu): master / worker / evaluator roles as host
+ * threads of one process, one GPU per role where available. ref: MPI_code/ (the reference's only native code).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct pdnn_fc_ps_config {
+    int n_dims;                 /* number of entries of dims, e.g. 9 for 784-500-500-800-800-200-100-100-10 */
+    int dims[64];
+    int batch;                  /* reference: 128 */
+    float lr;                   /* reference: 1e-3 */
+    int n_workers;              /* reference: n_procs - 2 = 6 */
+    int n_to_collect;           /* reference: n_procs - 2 - 4 = 2 */
+    int n_train_iters;          /* reference N_TRAIN_ITERS: 100 */
+    int shortcircuit;           /* reference SHORTCIRCUIT: workers abandon a step when a newer one is published */
+    int generate_timeline;      /* reference GENERATE_TIMELINE: outfiles/timeline_out_<scheme> */
+    int with_evaluator;         /* run the evaluator role (outfiles/time_loss_out_<scheme>: step time_ms loss err) */
+    int eval_batches;
+    unsigned long long delay_worker_mask;  /* bit w set: worker w sleeps delay_us_per_layer before each backward layer */
+    long long delay_us_per_layer;
+    unsigned seed;
+    int synthetic_examples;     /* size of the synthetic set used when data_dir has no MNIST IDX files */
+    int max_devices;            /* 0 = use every visible GPU */
+    char data_dir[256];
+    char out_dir[256];
+} pdnn_fc_ps_config_t;
+
+typedef struct pdnn_fc_ps_result {
+    int steps;
+    double total_ms, mean_step_ms;
+    long long gradients_accepted, gradients_dropped_stale, steps_abandoned;
+    double avg_gradients_per_step;   /* reference visualize_timeline.py: average #gradients received per step */
+    float first_loss, final_loss, first_err, final_err;
+    char scheme[128];                /* reference scheme_full_name(): SyncReplicasWithBackup<k>_<n>[_shortcircuit] */
+} pdnn_fc_ps_result_t;
+
+int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* result);
+int pdnn_fc_ps_selftest(int iters, float* first_loss, float* last_loss);
+
 #ifdef __cplusplus
 }
 #endif

@@ -41,6 +41,27 @@ class PSMaster(C.Structure):
     ]
 
 
+class FcPsConfig(C.Structure):
+    """Mirror of pdnn_fc_ps_config_t."""
+    _fields_ = [
+        ("n_dims", C.c_int), ("dims", C.c_int * 64), ("batch", C.c_int), ("lr", C.c_float), ("n_workers", C.c_int),
+        ("n_to_collect", C.c_int), ("n_train_iters", C.c_int), ("shortcircuit", C.c_int), ("generate_timeline", C.c_int),
+        ("with_evaluator", C.c_int), ("eval_batches", C.c_int), ("delay_worker_mask", C.c_ulonglong),
+        ("delay_us_per_layer", C.c_longlong), ("seed", C.c_uint), ("synthetic_examples", C.c_int), ("max_devices", C.c_int),
+        ("data_dir", C.c_char * 256), ("out_dir", C.c_char * 256),
+    ]
+
+
+class FcPsResult(C.Structure):
+    """Mirror of pdnn_fc_ps_result_t."""
+    _fields_ = [
+        ("steps", C.c_int), ("total_ms", C.c_double), ("mean_step_ms", C.c_double), ("gradients_accepted", C.c_longlong),
+        ("gradients_dropped_stale", C.c_longlong), ("steps_abandoned", C.c_longlong), ("avg_gradients_per_step", C.c_double),
+        ("first_loss", C.c_float), ("final_loss", C.c_float), ("first_err", C.c_float), ("final_err", C.c_float),
+        ("scheme", C.c_char * 128),
+    ]
+
+
 _P, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint32
 
 # name -> argtypes (stream pointer included where the C function takes one)
@@ -96,6 +117,9 @@ _SIGS = {
     "pdnn_ipc_open_handle": [_P, C.POINTER(C.c_void_p)],
     "pdnn_ipc_close": [_P],
     "pdnn_enable_peer_access": [_I],
+    "pdnn_bn_fwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _F, _F, _I, _P],
+    "pdnn_fc_ps_run": [C.POINTER(FcPsConfig), C.POINTER(FcPsResult)],
+    "pdnn_fc_ps_selftest": [_I, C.POINTER(C.c_float), C.POINTER(C.c_float)],
 }
 
 
