@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--grad-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--inject-delay", default="", help="straggler spec, e.g. 'const:ranks=1,2,3:ms=5' (see parallel/delays.py)")
     ap.add_argument("--n-buckets", type=int, default=8)
+    ap.add_argument("--master-only", action="store_true", help="rank 0 is master-only as in the reference (n = N-1 workers)")
+    ap.add_argument("--interval-ms", type=float, default=0.0, help="interval policy: the master closes each step after this deadline")
+    ap.add_argument("--worker-times-cdf", action="store_true", help="report the per-(worker, step) time distribution (TF study)")
     return ap.parse_args()
 
 
@@ -116,8 +119,8 @@ def main():
     B = args.batch_size
     delay_fn = parse_delay_spec(args.inject_delay) if args.inject_delay else None
     ps = B200ParameterServer(args.network, B, rank, world, lr=args.lr, momentum=args.momentum,
-                             num_aggregate=args.num_aggregate or None, grad_dtype=args.grad_dtype, colocate=True,
-                             n_buckets=args.n_buckets, delay_fn=delay_fn, group=group, device=dev)
+                             num_aggregate=args.num_aggregate or None, grad_dtype=args.grad_dtype, colocate=not (args.master_only and world > 1),
+                             n_buckets=args.n_buckets, delay_fn=delay_fn, group=group, device=dev, deadline_ms=args.interval_ms)
     chw = ps.net.in_chw
     gen = torch.Generator().manual_seed(1234 + rank)
     # synthetic CIFAR-10-shape data: raw 0..255 pixels like the reference reader (cifar10.py:167-199), 4 batches in rotation
@@ -162,7 +165,8 @@ def main():
             main.wait_event(ev_ready[cur])
             loss = ps.train_step(stage_x[cur], stage_y[cur])
             ev_free[cur].record(main)
-            loss_host.copy_(loss, non_blocking=True)
+            if loss is not None:
+                loss_host.copy_(loss, non_blocking=True)
             main.synchronize()            # the user reads the step's loss: a real D2H round trip per step
             losses.append(float(loss_host))
         return losses
@@ -191,7 +195,22 @@ def main():
     sync_all()
     launches = _lib.launch_count()
     total_ms = s.elapsed_time(e)
-    per_step = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps))
+    per_step_raw = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    per_step = sorted(per_step_raw)
+    cdf = None
+    if args.worker_times_cdf:
+        # per-(worker, iteration) times as in the reference's compute-time study (distributed_TF/tools/benchmark.py:60-111)
+        mine = torch.tensor(per_step_raw, device=dev, dtype=torch.float64)
+        allt = [torch.empty_like(mine) for _ in range(world)] if world > 1 else [mine]
+        if world > 1:
+            dist.all_gather(allt, mine)
+        if rank == 0:
+            from pytorch_distributed_nn_b200.parallel.delays import summarize_ms
+            mat = torch.stack(allt).cpu()                        # [worker][iteration]
+            per_iter = mat.max(dim=0).values.tolist()
+            cdf = {"all": summarize_ms(mat.flatten().tolist()),
+                   "per_iteration_slowest_worker": summarize_ms(per_iter),
+                   "per_worker_mean_ms": [float(v) for v in mat.mean(dim=1)]}
 
     # ---- timed region 2: end to end (H2D inputs from pinned memory + D2H loss every step) ----
     sync_all()
@@ -210,7 +229,7 @@ def main():
     total_ms, e2e_ms, p50, p99 = [float(v) for v in t.tolist()]
     res = ps.last_result() if rank == 0 else None
     if rank == 0:
-        gb = B * world
+        gb = B * ps.n_workers
         value = gb * args.steps / (total_ms / 1e3)
         e2e_value = gb * args.steps / (e2e_ms / 1e3)
         h2d = B * chw[0] * chw[1] * chw[2] * 4 + B * 8
@@ -222,7 +241,8 @@ def main():
             "impl": "ours",
             "config": {"model": args.network, "dataset_shape": "CIFAR-10 (3x32x32, 10 classes)" if chw[0] == 3 else "MNIST (1x28x28)",
                        "global_batch": gb, "per_worker_batch": B, "seq_len": None,
-                       "parallelism": f"ps-dp{world} (master+worker colocated on GPU0, k={ps.k} of n={ps.n_workers})",
+                       "parallelism": (f"ps-dp{ps.n_workers} (master+worker colocated on GPU0, k={ps.k} of n={ps.n_workers})" if ps.colocate else
+                                       f"ps-dp{ps.n_workers} (GPU0 master-only as in the reference, k={ps.k} of n={ps.n_workers})"),
                        "optimizer": f"momentum-SGD lr={args.lr} mu={args.momentum} (fp32 master weights)",
                        "grad_wire_dtype": args.grad_dtype, "inject_delay": args.inject_delay or "none",
                        "l2_policy": "working set (activations >> 126 MB L2 at batch 1024; 4 input batches rotate) exceeds L2"},
@@ -233,6 +253,8 @@ def main():
             "last_master_result": {"selected_mask": res[0], "kill_mask": res[1], "n_received": res[2], "step": res[3]},
             "clocks": clocks,
         }
+        if cdf is not None:
+            out["worker_times_cdf"] = cdf
         print(json.dumps(out))
     ps.close()
     if world > 1:

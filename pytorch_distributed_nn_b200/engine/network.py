@@ -265,6 +265,57 @@ class Network:
         return self.loss
 
 
+class FlatParams:
+    """A parameter vector without layers: the object the parameter-server kernels are benchmarked with
+    (push / aggregate / broadcast sweeps, BASELINE config 5). ``train_step`` just declares every bucket ready."""
+
+    def __init__(self, n_params: int, dtype=BF16, device="cuda", n_buckets: int = 1, external_w=None):
+        self.name = f"Flat{n_params}"
+        self.total = (n_params + ALIGN - 1) // ALIGN * ALIGN
+        self.dtype = dtype
+        self.device = torch.device(device)
+        self.in_chw = (1, 1, 1)
+        self.num_classes = 1
+        dev = self.device
+        self.w32 = torch.zeros(self.total, device=dev, dtype=F32)
+        self.w = external_w if external_w is not None else torch.zeros(self.total, device=dev, dtype=dtype)
+        self.g = torch.zeros(self.total, device=dev, dtype=F32)
+        self.loss = torch.zeros(1, device=dev, dtype=F32)
+        self.on_bucket = None
+        n_buckets = max(1, n_buckets)
+        step = (self.total // n_buckets + ALIGN - 1) // ALIGN * ALIGN
+        self.buckets, end = [], self.total
+        while end > 0:
+            start = max(0, end - step)
+            self.buckets.append(Bucket(len(self.buckets), start, end, []))
+            end = start
+        self.param_list = []
+
+    def init_parameters(self, seed=0):
+        if self.device.type != "meta":
+            g = torch.Generator(device="cpu").manual_seed(seed)
+            self.w32.copy_(torch.randn(self.total, generator=g))
+            if self.w.dtype == BF16:
+                self.w[: self.total].copy_(self.w32)
+            elif self.w is not self.w32:
+                self.w[: self.total].copy_(self.w32)
+
+    def prepare(self):
+        pass
+
+    def load_state_dict(self, sd, strict=True):
+        self.w32.copy_(sd["flat"])
+
+    def state_dict(self):
+        return OrderedDict(flat=self.w32.clone())
+
+    def train_step(self, x=None, labels=None):
+        for b in self.buckets:
+            if self.on_bucket is not None:
+                self.on_bucket(b)
+        return self.loss
+
+
 # -------------------------------------------------------------------------------------------------
 # builders (architectures: reference pytorch_code/model_ops/lenet.py:12-33, resnet.py:67-113; VGG is the
 # north-star addition, kuangliu CIFAR variant with BatchNorm)
@@ -379,6 +430,8 @@ def build_mlp(dims, batch, device="cuda", n_buckets=4, activation="sigmoid", ext
 
 def build_network(name: str, batch: int, device="cuda", n_buckets: int = 8, external_w=None) -> Network:
     key = name.replace("Split", "")
+    if key.startswith("Flat"):
+        return FlatParams(int(key[4:]), BF16, device, n_buckets, external_w=external_w)
     if key in ("LeNet",):
         return build_lenet(batch, device, min(n_buckets, 2), external_w=external_w)
     if key in ("ResNet", "Resnet"):
