@@ -229,7 +229,7 @@ def main():
     total_ms, e2e_ms, p50, p99 = [float(v) for v in t.tolist()]
     res = ps.last_result() if rank == 0 else None
     if rank == 0:
-        gb = B * ps.n_workers
+        gb = B * ps.k            # images whose gradients are applied per step (k of n sets; k = n without stragglers)
         value = gb * args.steps / (total_ms / 1e3)
         e2e_value = gb * args.steps / (e2e_ms / 1e3)
         h2d = B * chw[0] * chw[1] * chw[2] * 4 + B * 8
