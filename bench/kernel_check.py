@@ -164,6 +164,33 @@ def conv_fprop():
 
 
 @case
+def conv_halo():
+    F = _F()
+    ok = True
+    for (n, h, c, k) in [(2, 32, 64, 64), (3, 16, 128, 128), (4, 16, 64, 128), (2, 32, 128, 64), (5, 8, 64, 64)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        w = (torch.randn(k, 3, 3, c, device="cuda") / (3 * c ** 0.5)).bfloat16()
+        bias = torch.randn(k, device="cuda")
+        res = torch.randn(n, h, h, k, device="cuda").bfloat16()
+        assert F.conv_halo_supported(x.shape, k)
+        out = F.conv_halo_fprop(x, w, bias=bias, residual=res, relu=True)
+        ref = torch.relu(_conv_ref(x, w, 1) + bias + res.float())
+        ok &= report(f"conv_halo[n{n} {h}x{h} c{c} k{k}]", rel_err(out, ref), 1.5e-2)
+    for (n, h, c, k) in [(256, 32, 64, 64), (256, 16, 128, 128)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        w = (torch.randn(k, 3, 3, c, device="cuda") / 24).bfloat16()
+        out = torch.empty(n, h, h, k, device="cuda", dtype=torch.bfloat16)
+        ms = time_ms(lambda: F.conv_halo_fprop(x, w, out=out))
+        ms_old = time_ms(lambda: F.conv_fprop(x, w, pad=1, out=out))
+        xc = x.permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last)
+        wc = w.permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last)
+        cms = time_ms(lambda: torch.nn.functional.conv2d(xc, wc, padding=1))
+        fl = 2 * n * h * h * k * 9 * c
+        print(f"PERF conv_halo n{n} {h}x{h} c{c} k{k} halo_ms={ms:.3f} ({fl / ms / 1e9:.0f} TF) generic_ms={ms_old:.3f} cudnn_ms={cms:.3f}", flush=True)
+    return ok
+
+
+@case
 def conv_dgrad():
     F = _F()
     ok = True

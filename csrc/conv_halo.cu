@@ -1,0 +1,316 @@
+// 3x3 stride-1 pad-1 convolution with halo reuse and resident filters (tcgen05 / TMEM / TMA, sm_100a).
+//
+// The generic implicit-GEMM path (gemm_tcgen05.cu, OP_CONVK) fetches one shifted activation box per filter tap, i.e.
+// every input element travels L2 -> shared memory nine times, and re-fetches the filter tile for every output tile.
+// For the early ResNet / VGG stages (C = 64 / 128, 32x32 and 16x16 maps) that traffic, not the tensor pipe, is the
+// limit (ncu: 19% tensor active, see profiles/). Here:
+//   * ONE TMA box per (tile, 64-channel block) brings a zero-padded halo image [rows][W+2][64ch] into shared memory
+//     (out-of-bounds columns / rows are zero-filled by TMA: that IS the padding);
+//   * in that padded-flat space the input of tap (r, s) for output position p is position p + (r-1)(W+2) + (s-1):
+//     a pure shift, so all nine A operands are views of the same buffer -- the UMMA descriptor start address moves by
+//     multiples of 128 bytes and its base-offset field carries the swizzle phase;
+//   * the filter bank of this CTA's 64 output channels (9 taps x C/64 blocks x 8 KiB) is loaded once and stays
+//     resident while the persistent CTA walks its tiles.
+// Output positions that fall on the two padding columns of the padded-flat space are computed and discarded.
+#include "common.cuh"
+#include "../include/pdnn_b200.h"
+
+namespace pdnn {
+
+struct HaloParams {
+    int batch, H, W, C, Kout;
+    int Wp;              // W + 2
+    int Rb;              // halo rows per box
+    int tiles_per_img;   // ceil(H * Wp / 128)
+    int KB;              // C / 64
+    int n_cblocks;       // Kout / 64
+    int stage_bytes;     // Rb * Wp * 128 rounded up to 1024
+    int stages;
+    void* out;
+    long long ldo;
+    int relu;
+    const float* bias;
+    const __nv_bfloat16* residual;
+    const uint32_t* guard_closed;
+    const uint32_t* guard_step;
+};
+
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr) {
+    // K-major, 128B swizzle, SBO = 1024 (8 rows of 128 B); the start address may sit anywhere on a 128-byte row
+    // boundary (+ the 32-byte K step inside the row): base_offset = address bits [7,10) gives the swizzle phase.
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;                          // LBO (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;                // SBO
+    d |= (uint64_t)1 << 46;                          // descriptor version
+    d |= (uint64_t)((saddr >> 7) & 7) << 49;         // base offset
+    d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
+    return d;
+}
+
+constexpr int HALO_THREADS = 256;
+constexpr int HALO_BN = 64;
+
+__global__ void __launch_bounds__(HALO_THREADS, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
+    if (p.guard_closed != nullptr) {
+        __shared__ int s_abort;
+        if (threadIdx.x == 0) s_abort = ld_relaxed_sys(p.guard_closed) >= ld_relaxed_sys(p.guard_step);
+        __syncthreads();
+        if (s_abort) return;
+    }
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t smem_base = smem_u32(smem);
+    const int w_bytes = 9 * p.KB * 8192;
+    const uint32_t w_base = smem_base;
+    const uint32_t a_base = smem_base + w_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + w_bytes + p.stages * p.stage_bytes);
+    const uint32_t bar_base = smem_u32(bars);
+    // barrier slots: [0..S) full, [S..2S) empty, 2S..2S+1 tmem full, 2S+2..2S+3 tmem empty, 2S+4 weights
+    const int S = p.stages;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + 2 + a); };
+    const uint32_t wbar = bar_base + 8u * (2 * S + 4);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 5);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmX);
+        tma_prefetch_desc(&tmW);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        mbar_init(wbar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(smem_u32(tmem_slot), 2 * HALO_BN);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // work split: CTA -> (output-channel block, strided subset of tiles)
+    const int cb = blockIdx.x % p.n_cblocks;
+    const int cta_in_cb = blockIdx.x / p.n_cblocks;
+    const int ctas_per_cb = (gridDim.x - cb + p.n_cblocks - 1) / p.n_cblocks;
+    const int total_tiles = p.batch * p.tiles_per_img;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // resident filter bank of this CTA's 64 output channels
+            mbar_expect_tx(wbar, (uint32_t)w_bytes);
+            for (int tap = 0; tap < 9; ++tap)
+                for (int kb = 0; kb < p.KB; ++kb)
+                    tma_load_2d(w_base + (tap * p.KB + kb) * 8192, &tmW, wbar, tap * p.C + kb * 64, cb * HALO_BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+                const int n = tile / p.tiles_per_img;
+                const int p0 = (tile - n * p.tiles_per_img) * 128;
+                // first halo row: floor((p0 - Wp - 1) / Wp) in padded-flat rows == image row (p0-Wp-1)/Wp - 0; row r of the
+                // padded-flat space corresponds to image row r - 1 for the INPUT (one row of top padding)
+                int num = p0 - p.Wp - 1;
+                const int fl = num >= 0 ? num / p.Wp : -((-num + p.Wp - 1) / p.Wp);
+                const int h_lo = fl;            // input image row of the first box row, see kernel notes below
+                for (int kb = 0; kb < p.KB; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1);
+                    const uint32_t fb = full_bar(stage);
+                    mbar_expect_tx(fb, (uint32_t)(p.Rb * p.Wp * 128));
+                    tma_load_4d(a_base + stage * p.stage_bytes, &tmX, fb, kb * 64, -1, h_lo, n);
+                    if (++stage == S) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        constexpr uint32_t idesc = make_idesc_bf16(128, HALO_BN, 0, 0);
+        mbar_wait(wbar, 0);
+        tc_fence_after();
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+            const int n = tile / p.tiles_per_img;
+            const int p0 = (tile - n * p.tiles_per_img) * 128;
+            int num = p0 - p.Wp - 1;
+            const int fl = num >= 0 ? num / p.Wp : -((-num + p.Wp - 1) / p.Wp);
+            // Output position q (row = q / Wp, padded column = q % Wp, pixel w = column - 1) reads, for tap (r, s), the
+            // input pixel (row + r - 1, w + s - 1) = padded-flat input position (row + r - 1 + 1) * Wp + (w + s - 1 + 1)
+            // relative to an input space with one padding row on top: q + r * Wp + (s - 1) ... expressed against a box
+            // whose first row is input row h_lo: index = q + (r - 1 - h_lo) * Wp + (s - 1).
+            const int origin = p0 - fl * p.Wp;      // >= Wp + 1
+            mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * HALO_BN;
+            for (int kb = 0; kb < p.KB; ++kb) {
+                mbar_wait(full_bar(stage), phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t sa = a_base + stage * p.stage_bytes;
+#pragma unroll 1
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const int r = tap / 3, s = tap - r * 3;
+                        const uint32_t a_tap = sa + (uint32_t)(origin + (r - 1) * p.Wp + (s - 1)) * 128u;
+                        const uint32_t b_tap = w_base + (tap * p.KB + kb) * 8192;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            umma_bf16_ss(tmem_d, make_smem_desc_sw128_shifted(a_tap + j * 32), make_smem_desc_sw128(b_tap + j * 32, 16, 1024),
+                                         idesc, (kb > 0 || tap > 0 || j > 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(empty_bar(stage));
+                    if (kb == p.KB - 1) umma_commit(tfull_bar(acc));
+                }
+                __syncwarp();
+                if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    } else if (warp >= 4) {
+        const int ew = warp & 3;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+            const int n = tile / p.tiles_per_img;
+            const int q = (tile - n * p.tiles_per_img) * 128 + ew * 32 + lane;
+            const int row = q / p.Wp;
+            const int colp = q - row * p.Wp;
+            const bool valid = row < p.H && colp >= 1 && colp <= p.W;
+            const long long pix = ((long long)n * p.H + row) * p.W + (colp - 1);
+            mbar_wait(tfull_bar(acc), acc_phase);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < HALO_BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + acc * HALO_BN + c * 32, v);
+                tmem_ld_wait();
+                if (!valid) continue;
+                const int col0 = cb * HALO_BN + c * 32;
+                float f[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+                if (p.bias != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + col0 + i);
+                }
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.ldo + col0;
+                if (p.residual != nullptr) {
+                    const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.ldo + col0);
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        const uint4 u = rp[q4];
+                        float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+                        f[q4 * 8 + 0] += a.x; f[q4 * 8 + 1] += a.y; f[q4 * 8 + 2] += b.x; f[q4 * 8 + 3] += b.y;
+                        f[q4 * 8 + 4] += cc.x; f[q4 * 8 + 5] += cc.y; f[q4 * 8 + 6] += d.x; f[q4 * 8 + 7] += d.y;
+                    }
+                }
+                if (p.relu) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+                }
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    uint4 w;
+                    w.x = pack_bf16x2(f[q4 * 8 + 0], f[q4 * 8 + 1]);
+                    w.y = pack_bf16x2(f[q4 * 8 + 2], f[q4 * 8 + 3]);
+                    w.z = pack_bf16x2(f[q4 * 8 + 4], f[q4 * 8 + 5]);
+                    w.w = pack_bf16x2(f[q4 * 8 + 6], f[q4 * 8 + 7]);
+                    *reinterpret_cast<uint4*>(o + q4 * 8) = w;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 2 * HALO_BN);
+    }
+}
+
+}  // namespace pdnn
+
+using namespace pdnn;
+
+int pdnn_make_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const long long* dims, const long long* strides_elems,
+                        const int* box);   // gemm_tcgen05.cu
+
+extern "C" int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout, int R, int S, int pad) {
+    if (R != 3 || S != 3 || pad != 1) return 0;
+    if (C != 64 && C != 128) return 0;
+    if (Kout % 64 != 0) return 0;
+    const int Wp = W + 2;
+    const int Rb = (3 * Wp + 128) / Wp + 1;
+    if (Wp > 256 || Rb > 256) return 0;
+    const int stage_bytes = (Rb * Wp * 128 + 1023) / 1024 * 1024;
+    const int w_bytes = 9 * (C / 64) * 8192;
+    const int stages = (227 * 1024 - 2048 - w_bytes) / stage_bytes;
+    if (stages < 2) return 0;
+    if (W < 8 || H < 4) return 0;     // small maps waste most of a 128-position tile on padding: generic path is better
+    return 1;
+}
+
+extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                         const pdnn_epilogue_t* epi, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(pdnn_conv_halo_supported(batch, H, W, C, Kout, 3, 3, 1), "conv_halo: unsupported geometry (C=%d Kout=%d %dx%d)", C, Kout, H, W);
+    PDNN_REQUIRE(epi != nullptr && epi->out != nullptr && epi->out_mode == 0, "conv_halo: bf16 output required");
+    PDNN_REQUIRE(epi->ldo % 8 == 0, "conv_halo: ldo must be a multiple of 8");
+    HaloParams p{};
+    p.batch = batch; p.H = H; p.W = W; p.C = C; p.Kout = Kout;
+    p.Wp = W + 2;
+    p.Rb = (3 * p.Wp + 128) / p.Wp + 1;
+    p.tiles_per_img = (H * p.Wp + 127) / 128;
+    p.KB = C / 64;
+    p.n_cblocks = Kout / 64;
+    p.stage_bytes = (p.Rb * p.Wp * 128 + 1023) / 1024 * 1024;
+    const int w_bytes = 9 * p.KB * 8192;
+    p.stages = (227 * 1024 - 2048 - w_bytes) / p.stage_bytes;
+    if (p.stages > 6) p.stages = 6;
+    p.out = epi->out; p.ldo = epi->ldo; p.relu = epi->relu; p.bias = epi->bias;
+    p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
+    p.guard_closed = epi->guard_closed; p.guard_step = epi->guard_step;
+    CUtensorMap tmX, tmW;
+    {
+        long long dims[4] = {C, W, H, batch};
+        long long str[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int box[4] = {64, p.Wp, p.Rb, 1};
+        if (int rc = pdnn_make_tmap_bf16(&tmX, x, 4, dims, str, box)) return rc;
+        long long wd[2] = {9ll * C, Kout};
+        long long ws[2] = {1, 9ll * C};
+        int wb[2] = {64, 64};
+        if (int rc = pdnn_make_tmap_bf16(&tmW, wgt, 2, wd, ws, wb)) return rc;
+    }
+    const int smem = w_bytes + p.stages * p.stage_bytes + 256 + 1024;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        PDNN_CUDA_CHECK(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem = smem;
+    }
+    int sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    int grid = sms / p.n_cblocks * p.n_cblocks;
+    const int total_units = batch * p.tiles_per_img * p.n_cblocks;
+    if (grid > total_units) grid = (total_units / p.n_cblocks) * p.n_cblocks;
+    if (grid < p.n_cblocks) grid = p.n_cblocks;
+    if (epi->max_ctas > 0 && grid > epi->max_ctas) grid = (epi->max_ctas / p.n_cblocks) * p.n_cblocks;
+    if (grid < p.n_cblocks) grid = p.n_cblocks;
+    conv_halo_kernel<<<grid, HALO_THREADS, smem, stream>>>(tmX, tmW, p);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}

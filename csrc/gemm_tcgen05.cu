@@ -472,6 +472,12 @@ static void finish_splits(GemmParams& p) {
 
 using namespace pdnn;
 
+// shared with conv_halo.cu
+int pdnn_make_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const long long* dims, const long long* strides_elems,
+                        const int* box) {
+    return pdnn::make_tmap_bf16(tm, base, rank, dims, strides_elems, box);
+}
+
 // ------------------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------------------

@@ -55,6 +55,14 @@ int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, 
 int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
                          int R, int S, int pad, const pdnn_epilogue_t* epi, void* stream);
 
+/* 3x3 / stride 1 / pad 1 convolution with halo reuse and resident filters (csrc/conv_halo.cu): one TMA halo box per
+ * tile instead of nine shifted boxes, filter bank resident in shared memory. C in {64, 128}, Kout % 64 == 0.
+ * pdnn_conv_halo_supported() tells whether a geometry qualifies; same epilogue options as pdnn_conv_fprop_bf16
+ * (bf16 output only). ref: the same nn.Conv2d call sites as pdnn_conv_fprop_bf16. */
+int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout, int R, int S, int pad);
+int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                              const pdnn_epilogue_t* epi, void* stream);
+
 /* Weight gradient of the same conv: dw[Kout][R][S][C] (fp32) += dy^T * im2col(x). out_mode must be 2.
  * ref: nn.Conv2d bwd-filter (same call sites). */
 int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout,

@@ -80,6 +80,22 @@ def conv_fprop(x, w, *, pad, out=None, bias=None, relu=False, residual=None, out
     return out
 
 
+def conv_halo_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
+    n, h, w, c = x_shape
+    return bool(_lib.lib().pdnn_conv_halo_supported(n, h, w, c, kout, R, S, pad))
+
+
+def conv_halo_fprop(x, w, *, out=None, bias=None, relu=False, residual=None):
+    """3x3/s1/p1 conv through the halo-reuse kernel (C in {64,128}): x [N,H,W,C] bf16, w [Kout,3,3,C] bf16."""
+    n, h, wd, c = x.shape
+    kout = w.shape[0]
+    if out is None:
+        out = torch.empty(n, h, wd, kout, device=x.device, dtype=BF16)
+    e = _epi(out, kout, 0, relu, 1.0, bias, residual)
+    call("pdnn_conv_halo_fprop_bf16", x, w, n, h, wd, c, kout, C.byref(e), stream_ptr())
+    return out
+
+
 def conv_wgrad(x, dy, *, R, S, pad, out=None, k_splits=0):
     """dw[Kout,R,S,C] (fp32) += dy^T * shifted(x); out must be zero-filled (or hold a running sum)."""
     n, h, wd, c = x.shape
