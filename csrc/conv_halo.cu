@@ -7,13 +7,16 @@
 //   * ONE TMA box per (tile, 64-channel block) brings a zero-padded halo image [rows][W+2][64ch] into shared memory
 //     (out-of-bounds columns / rows are zero-filled by TMA: that IS the padding);
 //   * in that padded-flat space the input of tap (r, s) for output position p is position p + (r-1)(W+2) + (s-1):
-//     a pure shift, so all nine A operands are views of the same buffer -- the UMMA descriptor start address moves by
-//     multiples of 128 bytes and its base-offset field carries the swizzle phase;
+//     a pure shift, so all nine A operands are views of the same buffer -- the UMMA descriptor start address simply
+//     moves by multiples of 128 bytes (measured on B200: the 128B-swizzle XOR is taken from the absolute shared-memory
+//     address, exactly as TMA wrote it, so the descriptor's base-offset field must stay 0; setting it to
+//     (addr >> 7) & 7 gives wrong data -- bench/kernel_check.py conv_halo_diag);
 //   * the filter bank of this CTA's 64 output channels (9 taps x C/64 blocks x 8 KiB) is loaded once and stays
 //     resident while the persistent CTA walks its tiles.
 // Output positions that fall on the two padding columns of the padded-flat space are computed and discarded.
 #include "common.cuh"
 #include "../include/pdnn_b200.h"
+#include <stdlib.h>
 
 namespace pdnn {
 
@@ -33,17 +36,19 @@ struct HaloParams {
     const __nv_bfloat16* residual;
     const uint32_t* guard_closed;
     const uint32_t* guard_step;
+    int use_base_offset;
 };
 
-__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr) {
-    // K-major, 128B swizzle, SBO = 1024 (8 rows of 128 B); the start address may sit anywhere on a 128-byte row
-    // boundary (+ the 32-byte K step inside the row): base_offset = address bits [7,10) gives the swizzle phase.
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr, int use_base_offset) {
+    // K-major, 128B swizzle, SBO = 1024 (8 rows of 128 B); the start address may sit on any 128-byte row boundary
+    // (+ the 32-byte K step inside the row). base_offset stays 0 (see the file header); the switch exists for the
+    // diagnostic only.
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
     d |= (uint64_t)1 << 16;                          // LBO (unused for swizzled K-major)
     d |= (uint64_t)(1024 >> 4) << 32;                // SBO
     d |= (uint64_t)1 << 46;                          // descriptor version
-    d |= (uint64_t)((saddr >> 7) & 7) << 49;         // base offset
+    if (use_base_offset) d |= (uint64_t)((saddr >> 7) & 7) << 49;         // base offset
     d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
     return d;
 }
@@ -160,7 +165,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                         const uint32_t b_tap = w_base + (tap * p.KB + kb) * 8192;
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            umma_bf16_ss(tmem_d, make_smem_desc_sw128_shifted(a_tap + j * 32), make_smem_desc_sw128(b_tap + j * 32, 16, 1024),
+                            umma_bf16_ss(tmem_d, make_smem_desc_sw128_shifted(a_tap + j * 32, p.use_base_offset), make_smem_desc_sw128(b_tap + j * 32, 16, 1024),
                                          idesc, (kb > 0 || tap > 0 || j > 0) ? 1u : 0u);
                         }
                     }
@@ -280,6 +285,10 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     p.out = epi->out; p.ldo = epi->ldo; p.relu = epi->relu; p.bias = epi->bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
     p.guard_closed = epi->guard_closed; p.guard_step = epi->guard_step;
+    {
+        const char* e = getenv("PDNN_HALO_BASE_OFFSET");
+        p.use_base_offset = e != nullptr ? atoi(e) : 0;
+    }
     CUtensorMap tmX, tmW;
     {
         long long dims[4] = {C, W, H, batch};

@@ -101,6 +101,10 @@ class Conv2d(Layer):
             self.mode = "simt"
         elif stride == 1 and 2 * pad == k - 1 and cin % 64 == 0 and self._tileable(n, h, w):
             self.mode = "implicit"
+            # fprop / dgrad through the halo-reuse kernel where it applies (C, Cout in {64,128}: the traffic-bound stages)
+            self.halo_f = net.use_halo and net.device.type == "cuda" and F.conv_halo_supported(in_shape, cout, k, k, pad)
+            self.halo_b = (not first) and net.use_halo and net.device.type == "cuda" and \
+                F.conv_halo_supported((n, h, w, cout), cin, k, k, pad)
         else:
             self.mode = "lowered"
         self.y = torch.empty(self.out_shape, device=dev, dtype=dt)
@@ -154,7 +158,10 @@ class Conv2d(Layer):
         w = self.weight.w
         bias = self.bias.wf if self.bias is not None else None
         if self.mode == "implicit":
-            F.conv_fprop(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, out=self.y, bias=bias)
+            if self.halo_f:
+                F.conv_halo_fprop(x, w.view(self.cout, self.k, self.k, self.cin), out=self.y, bias=bias)
+            else:
+                F.conv_fprop(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, out=self.y, bias=bias)
         elif self.mode == "lowered":
             col = self._col(x)
             wmat = self.w_pad if self.kpad != self.kdim else w.view(self.cout, self.kdim)
@@ -213,7 +220,10 @@ class Conv2d(Layer):
             return None
         # ---- data gradient
         if self.mode == "implicit":
-            F.conv_fprop(dy, self.w_t, pad=self.pad, out=self.dx, residual=dx_residual)
+            if self.halo_b:
+                F.conv_halo_fprop(dy, self.w_t, out=self.dx, residual=dx_residual)
+            else:
+                F.conv_fprop(dy, self.w_t, pad=self.pad, out=self.dx, residual=dx_residual)
             return self.dx
         if self.mode == "lowered":
             wmat = self.w_pad if self.kpad != self.kdim else self.weight.w.view(self.cout, self.kdim)

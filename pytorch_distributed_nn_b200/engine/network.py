@@ -14,6 +14,7 @@ as soon as every gradient of a bucket has been produced, while backward is still
 """
 from __future__ import annotations
 
+import os
 from collections import OrderedDict
 from typing import Callable, List, Optional
 
@@ -54,6 +55,7 @@ class Network:
         self.dlogits = None
         self.x_in = None
         self.keep_col = True   # keep im2col matrices of lowered convs for backward (memory for time)
+        self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
 
     # ---- construction ---------------------------------------------------------------------------
     def add(self, layer):
