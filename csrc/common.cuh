@@ -167,6 +167,28 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Predicated forms: the whole warp runs the (convergent) issue loop and only the instruction itself is predicated
+// on `issue` (non-zero in exactly one lane). Keeping the C++ control flow convergent lets ptxas hold descriptors in
+// uniform registers; with an `if (lane == 0)` around the loop it emits ELECT + 5x R2UR + a uniformisation loop per
+// MMA (~16 instructions, measured: the issuing thread, not the tensor pipe, became the bottleneck).
+__device__ __forceinline__ void umma_bf16_ss_pred(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                  uint32_t accumulate, uint32_t issue) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pred(uint32_t bar, uint32_t issue) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n"
+        ::"r"(bar), "r"(issue)
+        : "memory");
+}
 // tcgen05.commit: the mbarrier gets one arrival once every MMA issued so far by this thread retired.
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)

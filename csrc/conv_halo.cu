@@ -55,6 +55,11 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr,
 
 constexpr int HALO_THREADS = 256;
 constexpr int HALO_BN = 64;
+// With N = 64 one tcgen05.mma occupies the tensor pipe for ~32 cycles, but a single thread needs ~90 cycles to issue
+// one (descriptor moves into uniform registers; measured with ncu: tensor pipe 35% active, issuing warp 100% busy).
+// Three warps therefore issue for three different tiles at once, each into its own TMEM accumulator.
+constexpr int HALO_ISSUERS = 3;
+constexpr int HALO_NACC = 4;
 
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
@@ -72,14 +77,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     const uint32_t a_base = smem_base + w_bytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + w_bytes + p.stages * p.stage_bytes);
     const uint32_t bar_base = smem_u32(bars);
-    // barrier slots: [0..S) full, [S..2S) empty, 2S..2S+1 tmem full, 2S+2..2S+3 tmem empty, 2S+4 weights
+    // barrier slots: [0..S) full, [S..2S) empty, then NACC tmem-full, NACC tmem-empty, 1 weights
     const int S = p.stages;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * S + a); };
-    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + 2 + a); };
-    const uint32_t wbar = bar_base + 8u * (2 * S + 4);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 5);
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * S + HALO_NACC + a); };
+    const uint32_t wbar = bar_base + 8u * (2 * S + 2 * HALO_NACC);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 2 * HALO_NACC + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -89,12 +94,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        for (int a = 0; a < HALO_NACC; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
         mbar_init(wbar, 1);
         mbar_fence_init();
     }
     if (warp == 2) {
-        tmem_alloc(smem_u32(tmem_slot), 2 * HALO_BN);
+        tmem_alloc(smem_u32(tmem_slot), HALO_NACC * HALO_BN);
         tmem_relinquish();
     }
     tc_fence_before();
@@ -134,54 +139,64 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp <= HALO_ISSUERS) {
+        // ===================== MMA issuers (warps 1..3): issuer i owns the tiles with sequence number == i mod 3 =====
+        const int issuer = warp - 1;
         constexpr uint32_t idesc = make_idesc_bf16(128, HALO_BN, 0, 0);
+        // descriptor arithmetic: the upper word is constant, the lower word is (addr >> 4) | LBO, so moving the start
+        // address by `b` bytes is `lo += b >> 4`.
+        const uint32_t desc_hi = (uint32_t)(make_smem_desc_sw128(0, 16, 1024) >> 32);
+        int tap_off[9];
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) tap_off[tap] = ((tap / 3 - 1) * p.Wp + (tap % 3 - 1)) * 8;   // 128 B / 16
         mbar_wait(wbar, 0);
         tc_fence_after();
-        int stage = 0, acc = 0;
-        uint32_t phase = 0, acc_phase = 0;
-        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+        const uint32_t w_lo = (uint32_t)make_smem_desc_sw128(w_base, 16, 1024);
+        const uint32_t issue = lane == 0 ? 1u : 0u;
+        int seq = 0;
+        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
+            if (seq % HALO_ISSUERS != issuer) continue;
             const int n = tile / p.tiles_per_img;
             const int p0 = (tile - n * p.tiles_per_img) * 128;
             int num = p0 - p.Wp - 1;
             const int fl = num >= 0 ? num / p.Wp : -((-num + p.Wp - 1) / p.Wp);
-            // Output position q (row = q / Wp, padded column = q % Wp, pixel w = column - 1) reads, for tap (r, s), the
-            // input pixel (row + r - 1, w + s - 1) = padded-flat input position (row + r - 1 + 1) * Wp + (w + s - 1 + 1)
-            // relative to an input space with one padding row on top: q + r * Wp + (s - 1) ... expressed against a box
-            // whose first row is input row h_lo: index = q + (r - 1 - h_lo) * Wp + (s - 1).
-            const int origin = p0 - fl * p.Wp;      // >= Wp + 1
+            // Output position q = row * Wp + (w + 1) reads, for tap (r, s), input pixel (row + r - 1, w + s - 1), which sits
+            // at index q + (r - 1 - h_lo) * Wp + (s - 1) of a halo box whose first row is image row h_lo = fl and whose
+            // first column is w = -1.  origin = p0 - fl * Wp >= Wp + 1 keeps every index non-negative.
+            const int origin = p0 - fl * p.Wp;
+            const int acc = seq % HALO_NACC;
+            const uint32_t acc_phase = (uint32_t)(seq / HALO_NACC) & 1u;
             mbar_wait(tempty_bar(acc), acc_phase ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * HALO_BN;
             for (int kb = 0; kb < p.KB; ++kb) {
+                const int unit = seq * p.KB + kb;
+                const int stage = unit % S;
+                const uint32_t phase = (uint32_t)(unit / S) & 1u;
                 mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t sa = a_base + stage * p.stage_bytes;
-#pragma unroll 1
-                    for (int tap = 0; tap < 9; ++tap) {
-                        const int r = tap / 3, s = tap - r * 3;
-                        const uint32_t a_tap = sa + (uint32_t)(origin + (r - 1) * p.Wp + (s - 1)) * 128u;
-                        const uint32_t b_tap = w_base + (tap * p.KB + kb) * 8192;
+                const uint32_t a_lo = (uint32_t)make_smem_desc_sw128(a_base + stage * p.stage_bytes + (uint32_t)origin * 128u, 16, 1024);
+                const uint32_t b_lo = w_lo + (uint32_t)kb * 512u;           // 8192 B per (tap, kb) tile
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            umma_bf16_ss(tmem_d, make_smem_desc_sw128_shifted(a_tap + j * 32, p.use_base_offset), make_smem_desc_sw128(b_tap + j * 32, 16, 1024),
-                                         idesc, (kb > 0 || tap > 0 || j > 0) ? 1u : 0u);
-                        }
+                for (int tap = 0; tap < 9; ++tap) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint64_t adesc = ((uint64_t)desc_hi << 32) | (uint32_t)(a_lo + tap_off[tap] + j * 2);
+                        const uint64_t bdesc = ((uint64_t)desc_hi << 32) | (uint32_t)(b_lo + (uint32_t)(tap * p.KB) * 512u + j * 2);
+                        umma_bf16_ss_pred(tmem_d, adesc, bdesc, idesc, (kb > 0 || tap > 0 || j > 0) ? 1u : 0u, issue);
                     }
-                    umma_commit(empty_bar(stage));
-                    if (kb == p.KB - 1) umma_commit(tfull_bar(acc));
                 }
+                umma_commit_pred(empty_bar(stage), issue);
+                if (kb == p.KB - 1) umma_commit_pred(tfull_bar(acc), issue);
                 __syncwarp();
-                if (++stage == S) { stage = 0; phase ^= 1; }
             }
-            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     } else if (warp >= 4) {
         const int ew = warp & 3;
-        int acc = 0;
-        uint32_t acc_phase = 0;
-        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+        int seq = 0;
+        for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
+            const int acc = seq % HALO_NACC;
+            const uint32_t acc_phase = (uint32_t)(seq / HALO_NACC) & 1u;
             const int n = tile / p.tiles_per_img;
             const int q = (tile - n * p.tiles_per_img) * 128 + ew * 32 + lane;
             const int row = q / p.Wp;
@@ -232,14 +247,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));
-            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 2 * HALO_BN);
+        tmem_dealloc(tmem_base, HALO_NACC * HALO_BN);
     }
 }
 
@@ -259,7 +273,7 @@ extern "C" int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout
     if (Wp > 256 || Rb > 256) return 0;
     const int stage_bytes = (Rb * Wp * 128 + 1023) / 1024 * 1024;
     const int w_bytes = 9 * (C / 64) * 8192;
-    const int stages = (227 * 1024 - 2048 - w_bytes) / stage_bytes;
+    const int stages = (227 * 1024 - 2560 - w_bytes) / stage_bytes;
     if (stages < 2) return 0;
     if (W < 8 || H < 4) return 0;     // small maps waste most of a 128-position tile on padding: generic path is better
     return 1;
@@ -280,7 +294,7 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     p.n_cblocks = Kout / 64;
     p.stage_bytes = (p.Rb * p.Wp * 128 + 1023) / 1024 * 1024;
     const int w_bytes = 9 * p.KB * 8192;
-    p.stages = (227 * 1024 - 2048 - w_bytes) / p.stage_bytes;
+    p.stages = (227 * 1024 - 2560 - w_bytes) / p.stage_bytes;
     if (p.stages > 6) p.stages = 6;
     p.out = epi->out; p.ldo = epi->ldo; p.relu = epi->relu; p.bias = epi->bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
@@ -300,7 +314,7 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
         int wb[2] = {64, 64};
         if (int rc = pdnn_make_tmap_bf16(&tmW, wgt, 2, wd, ws, wb)) return rc;
     }
-    const int smem = w_bytes + p.stages * p.stage_bytes + 256 + 1024;
+    const int smem = w_bytes + p.stages * p.stage_bytes + 512 + 1024;
     static int attr_smem = 0;
     if (smem > attr_smem) {
         PDNN_CUDA_CHECK(cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

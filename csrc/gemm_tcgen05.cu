@@ -212,22 +212,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int kit = k_begin; kit < k_end; ++kit) {
                 mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
-                if (lane == 0) {
+                {
+                    const uint32_t issue = lane == 0 ? 1u : 0u;
                     const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
                     const uint32_t sb = sa + L::A_BYTES;
+                    // K-major: advance 32 bytes inside the 128B swizzle row; SBO = 8 rows * 128 B.
+                    // MN-major: advance 16 K-rows (2048 B); SBO = 8 K-rows (1024 B); LBO = next 64-wide MN chunk (8192 B).
+                    // Only the low descriptor word changes with the start address (units of 16 bytes): one add per
+                    // operand per MMA instead of rebuilding the descriptor.
+                    const uint64_t a0 = A_MN ? make_smem_desc_sw128(sa, 8192, 1024) : make_smem_desc_sw128(sa, 16, 1024);
+                    const uint64_t b0 = B_MN ? make_smem_desc_sw128(sb, 8192, 1024) : make_smem_desc_sw128(sb, 16, 1024);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        // K-major: advance 32 bytes inside the 128B swizzle row; SBO = 8 rows * 128 B.
-                        // MN-major: advance 16 K-rows (2048 B); SBO = 8 K-rows (1024 B); LBO = next
-                        // 64-wide MN chunk (8192 B).
-                        const uint64_t adesc = A_MN ? make_smem_desc_sw128(sa + k * 2048, 8192, 1024)
-                                                    : make_smem_desc_sw128(sa + k * 32, 16, 1024);
-                        const uint64_t bdesc = B_MN ? make_smem_desc_sw128(sb + k * 2048, 8192, 1024)
-                                                    : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-                        umma_bf16_ss(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u);
+                        const uint64_t adesc = a0 + (uint64_t)(k * (A_MN ? 128 : 2));
+                        const uint64_t bdesc = b0 + (uint64_t)(k * (B_MN ? 128 : 2));
+                        umma_bf16_ss_pred(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u, issue);
                     }
-                    umma_commit(empty_bar(stage));
-                    if (kit == k_end - 1) umma_commit(tfull_bar(acc));
+                    umma_commit_pred(empty_bar(stage), issue);
+                    if (kit == k_end - 1) umma_commit_pred(tfull_bar(acc), issue);
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
