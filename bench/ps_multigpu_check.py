@@ -74,7 +74,9 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
             by_worker = {w: grads[ps._worker_rank(w)].cpu() for w in range(n_workers)}
             w_ref, m_ref, sel_o, killed_o = kofn_update(w_ref, m_ref, by_worker, selected, len(selected), n_workers, lr=lr, mu=mu)
             err = float((master_w.cpu() - w_ref).abs().max())
-            if err > 2e-5:
+            # the in-switch bf16 reduction rounds the SUM to bf16 once more than the oracle does
+            tol = 3e-4 if (ps.nvls_gather and grad_dtype == "bf16") else 2e-5
+            if err > tol:
                 ok = False
                 log.append(f"step {s}: master vs oracle max abs err {err:.3e}")
         # every worker's buffer == cast(master copy)
@@ -98,6 +100,8 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
             if sel != (1 << n_workers) - 1 or kill != 0:
                 ok = False
                 log.append(f"step {s}: expected all selected, got sel={sel:b} kill={kill:b}")
+    if rank == 0:
+        print(f"PSMODE k={ps.k}/{n_workers} grad={grad_dtype} colocate={colocate} nvls_broadcast={ps.nvls} nvls_gather={ps.nvls_gather}", flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if not ok:

@@ -144,6 +144,24 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
         const long long nth = (long long)gridDim.x * blockDim.x;
         for (long long i = tid; i < n4; i += nth) {
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (a.multicast_slots != nullptr && nsel == (uint32_t)a.n_workers) {
+                // all n sets contribute: one load-reduce through the NVLS multicast address sums the workers' local
+                // slots inside the switch (1x ingress instead of n x)
+                if (a.slot_is_bf16) {
+                    uint32_t r0, r1;
+                    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0, %1}, [%2];"
+                                 : "=r"(r0), "=r"(r1)
+                                 : "l"(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots) + i * 4)
+                                 : "memory");
+                    const float2 lo = unpack_bf16x2(r0), hi = unpack_bf16x2(r1);
+                    acc = make_float4(lo.x, lo.y, hi.x, hi.y);
+                } else {
+                    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(acc.x), "=f"(acc.y), "=f"(acc.z), "=f"(acc.w)
+                                 : "l"(reinterpret_cast<const float*>(a.multicast_slots) + i * 4)
+                                 : "memory");
+                }
+            } else
             for (int w = 0; w < a.n_workers; ++w) {
                 if (!(mask & (1u << w))) continue;
                 if (a.slot_is_bf16) {
@@ -300,7 +318,8 @@ extern "C" int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* resul
     PDNN_REQUIRE(args->n_workers >= 1 && args->n_workers <= PDNN_MAX_WORKERS, "ps_master_step: n_workers=%d out of range", args->n_workers);
     PDNN_REQUIRE(args->k >= 1 && args->k <= args->n_workers, "ps_master_step: k=%d must be in [1, %d]", args->k, args->n_workers);
     PDNN_REQUIRE(args->control != nullptr && args->master_w != nullptr && args->momentum != nullptr, "ps_master_step: missing buffers");
-    PDNN_REQUIRE(args->n % 4 == 0 || args->multicast_weights == nullptr, "ps_master_step: multicast path needs n %% 4 == 0");
+    PDNN_REQUIRE(args->n % 4 == 0 || (args->multicast_weights == nullptr && args->multicast_slots == nullptr),
+                 "ps_master_step: multicast paths need n %% 4 == 0");
     MasterArgs m;
     m.a = *args;
     m.result = result;

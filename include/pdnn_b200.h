@@ -173,6 +173,8 @@ typedef struct pdnn_ps_master {
     uint32_t* worker_ready[PDNN_MAX_WORKERS];/* peer pointers: weights_ready word of each worker */
     uint32_t* worker_closed[PDNN_MAX_WORKERS];/* peer pointers: step_closed word of each worker */
     void* multicast_weights;                 /* NVLS multicast address of the weight buffers or NULL */
+    const void* multicast_slots;             /* NVLS multicast address of the workers' LOCAL gradient slots or NULL: when set
+                                                (and all n are aggregated) the sum is one multimem.ld_reduce in the switch */
     float* master_w;                         /* fp32 master weights */
     float* momentum;                         /* fp32 momentum buffer */
     uint32_t* control;                       /* >= 64 words of zero-initialised master-local scratch */

@@ -33,7 +33,7 @@ class PSMaster(C.Structure):
     _fields_ = [
         ("slots", C.c_void_p * MAX_WORKERS), ("arrival_flags", C.c_void_p),
         ("worker_weights", C.c_void_p * MAX_WORKERS), ("worker_ready", C.c_void_p * MAX_WORKERS),
-        ("worker_closed", C.c_void_p * MAX_WORKERS), ("multicast_weights", C.c_void_p),
+        ("worker_closed", C.c_void_p * MAX_WORKERS), ("multicast_weights", C.c_void_p), ("multicast_slots", C.c_void_p),
         ("master_w", C.c_void_p), ("momentum", C.c_void_p), ("control", C.c_void_p),
         ("n", C.c_longlong), ("n_workers", C.c_int), ("k", C.c_int), ("slot_is_bf16", C.c_int),
         ("weights_are_bf16", C.c_int), ("avg_mode", C.c_int), ("lr", C.c_float), ("mu", C.c_float),

@@ -21,6 +21,7 @@ Nothing in the step touches the host: each rank simply enqueues its kernels; str
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 from typing import Callable, Optional
 
@@ -29,7 +30,7 @@ import torch
 from ..engine.network import Network, build_network
 from ..ops import _lib
 from ..ops import functional as F
-from .peer import PeerArena
+from .peer import PeerArena, make_arena
 from .protocol import AVG_MODES, STEP_START_
 
 U32 = 4
@@ -84,12 +85,18 @@ class B200ParameterServer:
         self.wbytes = total * (2 if wdtype == torch.bfloat16 else 4)
         self.slot_elem = 2 if self.grad_bf16 else 4
         slot_bytes = total * self.slot_elem
-        # symmetric size keeps the carve offsets identical on every rank (only rank 0's slots are used)
-        arena_bytes = 4096 + FLAG_WORDS * U32 + self.wbytes + 512 + self.n_workers * (slot_bytes + 256)
-        self.arena = PeerArena(arena_bytes, self.rank, self.world, self.device, group)
+        # symmetric size keeps the carve offsets identical on every rank (only rank 0's master-side slots are used)
+        arena_bytes = 4096 + FLAG_WORDS * U32 + self.wbytes + 512 + (self.n_workers + 1) * (slot_bytes + 256)
+        self.arena = make_arena(arena_bytes, self.rank, self.world, self.device, group,
+                                prefer_symmetric=os.environ.get("PDNN_NO_SYMM") != "1")
         self.off_flags = self.arena.carve(FLAG_WORDS * U32)
         self.off_w = self.arena.carve(self.wbytes)
+        self.off_gslot = self.arena.carve(slot_bytes)            # this rank's LOCAL gradient slot (NVLS gather mode)
         self.off_slots = [self.arena.carve(slot_bytes) for _ in range(self.n_workers)]
+        # NVLS (in-switch) paths: weights go out with one multimem.st; when every worker is aggregated the gradients
+        # come in with one multimem.ld_reduce over the workers' local slots instead of n pushed copies
+        self.nvls = bool(getattr(self.arena, "mc_ptr", 0)) and os.environ.get("PDNN_NO_NVLS") != "1"
+        self.nvls_gather = self.nvls and self.k == self.n_workers and self.deadline_ns == 0
         self.flags = self.arena.tensor(self.off_flags, FLAG_WORDS * U32, torch.int32)
         w_ext = self.arena.tensor(self.off_w, self.wbytes, wdtype)
         real_batch = batch if self.is_worker else self._min_batch(network)
@@ -111,7 +118,10 @@ class B200ParameterServer:
         self.step_word = self.flags[W_STEP: W_STEP + 1]
         if self.is_worker:
             w = self.worker_id
-            self._slot_ptr = self.arena.ptr(0, self.off_slots[w])          # my slot lives on the master (rank 0)
+            if self.nvls_gather:
+                self._slot_ptr = self.arena.ptr(self.rank, self.off_gslot)     # local slot, summed in the switch by the master
+            else:
+                self._slot_ptr = self.arena.ptr(0, self.off_slots[w])          # my slot lives on the master (rank 0)
             self._arrival_ptr = self._flag_ptr(0, M_ARRIVAL + w)
             last_bucket = net.buckets[-1].index
 
@@ -126,12 +136,13 @@ class B200ParameterServer:
             m = _lib.PSMaster()
             for w in range(self.n_workers):
                 r = self._worker_rank(w)
-                m.slots[w] = self.arena.ptr(0, self.off_slots[w])
+                m.slots[w] = self.arena.ptr(r, self.off_gslot) if self.nvls_gather else self.arena.ptr(0, self.off_slots[w])
                 m.worker_weights[w] = self.arena.ptr(r, self.off_w)
                 m.worker_ready[w] = self._flag_ptr(r, W_READY)
                 m.worker_closed[w] = self._flag_ptr(r, W_CLOSED)
             m.arrival_flags = self._flag_ptr(0, M_ARRIVAL)
-            m.multicast_weights = None
+            m.multicast_weights = self.arena.mc(self.off_w) if self.nvls else None
+            m.multicast_slots = self.arena.mc(self.off_gslot) if self.nvls_gather else None
             m.master_w = net.w32.data_ptr()
             m.momentum = self.momentum.data_ptr()
             m.control = self._flag_ptr(0, M_CONTROL)

@@ -91,3 +91,50 @@ class PeerArena:
             except Exception:
                 pass
             self.local = 0
+
+
+class SymmArena(PeerArena):
+    """Same interface as :class:`PeerArena`, but the allocation comes from torch's symmetric-memory allocator
+    (CUDA VMM + fabric handles), which also binds the arenas of all ranks to one NVLS **multicast** address:
+    a store to ``mc_ptr + offset`` lands in every rank's arena (the switch replicates it), and
+    ``multimem.ld_reduce`` on it returns the sum over all ranks computed inside the switch.
+    ``mc_ptr`` is 0 when the fabric has no multicast support; callers then use the unicast pointers."""
+
+    def __init__(self, nbytes: int, rank: int, world: int, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.nbytes = int((nbytes + 255) // 256 * 256)
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        self._cursor = 0
+        self._opened = []
+        self._buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        self._buf.zero_()
+        grp = group if group is not None else dist.group.WORLD
+        self._hdl = symm_mem.rendezvous(self._buf, grp.group_name if hasattr(grp, "group_name") else grp)
+        self.local = int(self._buf.data_ptr())
+        self.ptrs = [int(p) for p in list(self._hdl.buffer_ptrs)[:world]]
+        self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+
+    def mc(self, offset: int) -> int:
+        return self.mc_ptr + offset if self.mc_ptr else 0
+
+    def close(self):
+        self._hdl = None
+        self._buf = None
+        self.local = 0
+
+
+def make_arena(nbytes: int, rank: int, world: int, device, group=None, prefer_symmetric: bool = True):
+    """Symmetric (multicast-capable) arena when torch provides one for this job, CUDA-IPC arena otherwise."""
+    if world > 1 and prefer_symmetric:
+        try:
+            return SymmArena(nbytes, rank, world, device, group)
+        except Exception as ex:  # noqa: BLE001 -- any failure of the optional path falls back to plain IPC
+            import warnings
+            warnings.warn(f"symmetric memory unavailable ({ex!r}); using CUDA IPC peer arenas without multicast")
+    arena = PeerArena(nbytes, rank, world, device, group)
+    arena.mc_ptr = 0
+    arena.mc = lambda offset: 0
+    return arena
