@@ -187,3 +187,18 @@ def test_delay_kernel_busy_waits_and_aborts():
     e.record()
     torch.cuda.synchronize()
     assert s.elapsed_time(e) < 20.0
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_multi_gpu_parameter_server_checks():
+    """torchrun with one rank per GPU (2): all-n (incl. NVLS multicast / in-switch reduce when the fabric offers it),
+    bf16 wire, k-of-n with an injected device-side delay -- each compared with the oracle (bench/ps_multigpu_check.py)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29577", os.path.join(root, "bench", "ps_multigpu_check.py"), "--network", "LeNet"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("PSCHECK") >= 3 and "FAIL" not in r.stdout
