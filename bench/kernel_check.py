@@ -206,6 +206,31 @@ def conv_halo():
 
 
 @case
+def conv_halo_wgrad():
+    F = _F()
+    ok = True
+    for (n, h, c, k) in [(2, 32, 64, 64), (3, 16, 128, 128), (4, 16, 64, 128), (2, 32, 128, 64), (5, 8, 64, 64), (37, 32, 64, 64)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        dy = torch.randn(n, h, h, k, device="cuda").bfloat16()
+        assert F.conv_halo_wgrad_supported(x.shape, k)
+        w = torch.zeros(k, c, 3, 3, device="cuda", requires_grad=True)
+        y = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w, padding=1)
+        y.backward(dy.float().permute(0, 3, 1, 2))
+        ref = w.grad.permute(0, 2, 3, 1)
+        dw = F.conv_halo_wgrad(x, dy)
+        ok &= report(f"conv_halo_wgrad[n{n} {h}x{h} c{c} k{k}]", rel_err(dw, ref), 5e-3)
+    for (n, h, c, k) in [(256, 32, 64, 64), (256, 16, 128, 128)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        dy = torch.randn(n, h, h, k, device="cuda").bfloat16()
+        out = torch.zeros(k, 3, 3, c, device="cuda")
+        ms = time_ms(lambda: F.conv_halo_wgrad(x, dy, out=out))
+        ms_old = time_ms(lambda: F.conv_wgrad(x, dy, R=3, S=3, pad=1, out=out))
+        fl = 2 * n * h * h * k * 9 * c
+        print(f"PERF conv_halo_wgrad n{n} {h}x{h} c{c} k{k} halo_ms={ms:.3f} ({fl / ms / 1e9:.0f} TF) generic_ms={ms_old:.3f}", flush=True)
+    return ok
+
+
+@case
 def conv_dgrad():
     F = _F()
     ok = True

@@ -337,3 +337,263 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
+
+// =================================================================================================================
+// Weight gradient with halo reuse
+// =================================================================================================================
+// dW[k][r][s][c] = sum over (n, row, w) of dY[n, row, w, k] * X[n, row + r - 1, w + s - 1, c].
+// The reduction runs over positions, so both operands are MN-major (positions are the K dimension). A chunk of Hc
+// image rows is brought in ONCE per CTA step: dY as a padded-flat tile [Hc][W+2][64 ch] (TMA zero-fills the two
+// padding columns, so padding positions contribute nothing) and X as a halo [Hc+2][W+2][64 ch]. In that space tap
+// (r, s) is again a pure row shift of the B operand: index q + r (W+2) + (s - 1). A CTA owns one (cin block, cout
+// block, tap group) and keeps ALL accumulators of its taps in TMEM for its whole life (taps x 64 columns), walking
+// the (image, row chunk) list with split-K across CTAs; one fp32 red.add epilogue at the very end. Three issuer
+// warps drive different taps (= different accumulators) of the same chunk concurrently.
+namespace pdnn {
+
+struct HaloWgradParams {
+    int batch, H, W, C, Kout;
+    int Wp, Hc;            // W + 2 ; image rows per chunk (Hc * Wp is a multiple of 16)
+    int chunks_per_img;    // H / Hc
+    int KS;                // k16 steps per chunk = Hc * Wp / 16
+    int m_chunks;          // 1 (Kout tile of 64, rows 64..127 of the MMA alias rows 0..63) or 2 (Kout tile of 128)
+    int n_cin_blocks, n_cout_blocks;
+    int dy_bytes, halo_off, stage_bytes, stages;
+    int ctas_group_a;      // CTAs working on taps 0..5 ; the rest work on taps 6..8
+    float* out;            // [Kout][9 * C] fp32, red.add
+    const uint32_t* guard_closed;
+    const uint32_t* guard_step;
+};
+
+__global__ void __launch_bounds__(HALO_THREADS, 1)
+conv_halo_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const HaloWgradParams p) {
+    if (p.guard_closed != nullptr) {
+        __shared__ int s_abort;
+        if (threadIdx.x == 0) s_abort = ld_relaxed_sys(p.guard_closed) >= ld_relaxed_sys(p.guard_step);
+        __syncthreads();
+        if (s_abort) return;
+    }
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const uint32_t smem_base = smem_u32(smem);
+    const int S = p.stages;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S * p.stage_bytes);
+    const uint32_t bar_base = smem_u32(bars);
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (S + s); };
+    const uint32_t done_bar = bar_base + 8u * (2 * S);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * S + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // which (tap group, cin block, cout block) does this CTA accumulate, and which share of the chunks does it take?
+    const int combos = p.n_cin_blocks * p.n_cout_blocks;
+    const bool group_a = (int)blockIdx.x < p.ctas_group_a;
+    const int gidx = group_a ? blockIdx.x : blockIdx.x - p.ctas_group_a;
+    const int gsize = group_a ? p.ctas_group_a : (int)gridDim.x - p.ctas_group_a;
+    const int combo = gidx % combos;
+    const int part = gidx / combos;
+    const int parts = (gsize - combo + combos - 1) / combos;
+    const int cin_blk = combo % p.n_cin_blocks;
+    const int cout_blk = combo / p.n_cin_blocks;
+    const int tap0 = group_a ? 0 : 6;
+    const int ntaps = group_a ? 6 : 3;
+    const int total_chunks = p.batch * p.chunks_per_img;
+
+    // zero the guard rows around every halo buffer once: positions on the padding columns multiply a zero dY row with
+    // whatever sits one row before / after the halo, and that must not be a NaN bit pattern
+    {
+        const int halo_end = p.halo_off + (p.Hc + 2) * p.Wp * 128;
+        for (int s = 0; s < S; ++s) {
+            uint8_t* st = smem + s * p.stage_bytes;
+            for (int i = threadIdx.x; i < 1024 / 16; i += blockDim.x)
+                reinterpret_cast<uint4*>(st + p.halo_off - 1024)[i] = make_uint4(0, 0, 0, 0);
+            for (int i = threadIdx.x; i < (p.stage_bytes - halo_end) / 16; i += blockDim.x)
+                reinterpret_cast<uint4*>(st + halo_end)[i] = make_uint4(0, 0, 0, 0);
+        }
+    }
+    fence_proxy_async_smem();
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmDY);
+        tma_prefetch_desc(&tmX);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), HALO_ISSUERS); }
+        mbar_init(done_bar, HALO_ISSUERS);
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(smem_u32(tmem_slot), 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int halo_bytes = (p.Hc + 2) * p.Wp * 128;
+    const int dy_tile_bytes = p.Hc * p.Wp * 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int ch = part; ch < total_chunks; ch += parts) {
+                const int n = ch / p.chunks_per_img;
+                const int h0 = (ch - n * p.chunks_per_img) * p.Hc;
+                mbar_wait(empty_bar(stage), phase ^ 1);
+                const uint32_t fb = full_bar(stage);
+                const uint32_t sb = smem_base + stage * p.stage_bytes;
+                mbar_expect_tx(fb, (uint32_t)(p.m_chunks * dy_tile_bytes + halo_bytes));
+                for (int j = 0; j < p.m_chunks; ++j)
+                    tma_load_4d(sb + j * dy_tile_bytes, &tmDY, fb, cout_blk * (64 * p.m_chunks) + j * 64, -1, h0, n);
+                tma_load_4d(sb + p.halo_off, &tmX, fb, cin_blk * 64, -1, h0 - 1, n);
+                if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp <= HALO_ISSUERS) {
+        // issuer i drives taps tap0 + i, tap0 + i + 3 (group A) or tap0 + i (group B); accumulator column = local tap * 64
+        const int issuer = warp - 1;
+        constexpr uint32_t idesc = make_idesc_bf16(128, HALO_BN, 1, 1);     // both operands MN-major
+        const uint32_t issue = lane == 0 ? 1u : 0u;
+        // MN-major SW128 descriptors: SBO = 1024 (8 K-rows of 128 B); LBO = stride between 64-wide MN chunks. With a
+        // 64-wide Kout tile LBO = 0 makes MMA rows 64..127 alias rows 0..63 (ignored by the epilogue) instead of costing
+        // a second, empty dY tile.
+        const uint64_t a_hi_lbo = make_smem_desc_sw128(0, p.m_chunks == 2 ? (uint32_t)dy_tile_bytes : 0u, 1024);
+        const uint64_t b_hi_lbo = make_smem_desc_sw128(0, 0, 1024);
+        int stage = 0;
+        uint32_t phase = 0;
+        bool first = true;
+        for (int ch = part; ch < total_chunks; ch += parts) {
+            mbar_wait(full_bar(stage), phase);
+            tc_fence_after();
+            const uint32_t sb = smem_base + stage * p.stage_bytes;
+            const uint64_t a0 = a_hi_lbo + (uint64_t)((sb & 0x3FFFF) >> 4);
+            const uint64_t b0 = b_hi_lbo + (uint64_t)(((sb + p.halo_off) & 0x3FFFF) >> 4);
+            for (int lt = issuer; lt < ntaps; lt += HALO_ISSUERS) {
+                const int tap = tap0 + lt;
+                const int r = tap / 3, s = tap - r * 3;
+                const int shift = r * p.Wp + (s - 1);                       // rows of 128 B; >= -1 (guard row in front)
+                const uint32_t tmem_d = tmem_base + lt * HALO_BN;
+                const uint64_t b_tap = b0 + (uint64_t)(int64_t)(shift * 8);  // 128 B = 8 x 16 B
+#pragma unroll 4
+                for (int k = 0; k < p.KS; ++k) {
+                    umma_bf16_ss_pred(tmem_d, a0 + (uint64_t)(k * 128), b_tap + (uint64_t)(k * 128), idesc, (first && k == 0) ? 0u : 1u, issue);
+                }
+            }
+            umma_commit_pred(empty_bar(stage), issue);
+            __syncwarp();
+            first = false;
+            if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_pred(done_bar, issue);
+    } else if (warp >= 4) {
+        // ===================== epilogue: once, after every chunk of this CTA has been accumulated =====================
+        const int ew = warp & 3;
+        mbar_wait(done_bar, 0);
+        tc_fence_after();
+        const int krow = cout_blk * (64 * p.m_chunks) + ew * 32 + lane;
+        const bool row_ok = (ew * 32 + lane) < 64 * p.m_chunks && krow < p.Kout && part < total_chunks;
+        for (int lt = 0; lt < ntaps; ++lt) {
+            const int tap = tap0 + lt;
+#pragma unroll 1
+            for (int c = 0; c < HALO_BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + lt * HALO_BN + c * 32, v);
+                tmem_ld_wait();
+                if (!row_ok) continue;
+                float* o = p.out + (long long)krow * (9 * p.C) + tap * p.C + cin_blk * 64 + c * 32;
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + q * 4), "f"(__uint_as_float(v[q * 4])),
+                                 "f"(__uint_as_float(v[q * 4 + 1])), "f"(__uint_as_float(v[q * 4 + 2])), "f"(__uint_as_float(v[q * 4 + 3]))
+                                 : "memory");
+            }
+        }
+        tc_fence_before();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace pdnn
+
+static int halo_wgrad_geometry(int H, int W, int C, int Kout, HaloWgradParams* p) {
+    if (C != 64 && C != 128) return 0;
+    if (Kout % 64 != 0) return 0;
+    const int Wp = W + 2;
+    int Hc = 0;
+    for (int cand : {8, 16, 4}) {
+        if (H % cand == 0 && (cand * Wp) % 16 == 0 && cand * Wp <= 512 && cand + 2 <= 256) { Hc = cand; break; }
+    }
+    if (Hc == 0 || Wp > 256 || W < 8) return 0;
+    p->Wp = Wp; p->Hc = Hc;
+    p->chunks_per_img = H / Hc;
+    p->KS = Hc * Wp / 16;
+    p->m_chunks = (Kout % 128 == 0) ? 2 : 1;
+    p->n_cin_blocks = C / 64;
+    p->n_cout_blocks = Kout / (64 * p->m_chunks);
+    const int dy_tile = Hc * Wp * 128;
+    p->dy_bytes = (p->m_chunks * dy_tile + 1023) / 1024 * 1024;
+    p->halo_off = p->dy_bytes + 1024;                                 // 1 KiB zero guard in front of the halo
+    p->stage_bytes = (p->halo_off + (Hc + 2) * Wp * 128 + 1023) / 1024 * 1024 + 1024;   // + zero guard behind it
+    p->stages = (227 * 1024 - 2048) / p->stage_bytes;
+    if (p->stages > 4) p->stages = 4;
+    return p->stages >= 2;
+}
+
+extern "C" int pdnn_conv_halo_wgrad_supported(int batch, int H, int W, int C, int Kout, int R, int S, int pad) {
+    if (R != 3 || S != 3 || pad != 1) return 0;
+    HaloWgradParams p{};
+    return halo_wgrad_geometry(H, W, C, Kout, &p);
+}
+
+extern "C" int pdnn_conv_halo_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout, float* dw,
+                                         const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    HaloWgradParams p{};
+    PDNN_REQUIRE(halo_wgrad_geometry(H, W, C, Kout, &p), "conv_halo_wgrad: unsupported geometry (C=%d Kout=%d %dx%d)", C, Kout, H, W);
+    p.batch = batch; p.H = H; p.W = W; p.C = C; p.Kout = Kout;
+    p.out = dw;
+    p.guard_closed = guard_closed; p.guard_step = guard_step;
+    CUtensorMap tmDY, tmX;
+    {
+        long long dd[4] = {Kout, W, H, batch};
+        long long ds[4] = {1, Kout, (long long)W * Kout, (long long)H * W * Kout};
+        int db[4] = {64, p.Wp, p.Hc, 1};
+        if (int rc = pdnn_make_tmap_bf16(&tmDY, dy, 4, dd, ds, db)) return rc;
+        long long xd[4] = {C, W, H, batch};
+        long long xs[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int xb[4] = {64, p.Wp, p.Hc + 2, 1};
+        if (int rc = pdnn_make_tmap_bf16(&tmX, x, 4, xd, xs, xb)) return rc;
+    }
+    const int smem = p.stages * p.stage_bytes + 512 + 1024;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        PDNN_CUDA_CHECK(cudaFuncSetAttribute(conv_halo_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_smem = smem;
+    }
+    int sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    int grid = sms;
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+    const int combos = p.n_cin_blocks * p.n_cout_blocks;
+    if (grid < 2 * combos) grid = 2 * combos;
+    // taps 0..5 carry twice the MMA work of taps 6..8 but the same TMA traffic: 3 : 2 split of the CTAs, in whole combos
+    int a = grid * 3 / 5 / combos * combos;
+    if (a < combos) a = combos;
+    if (grid - a < combos) a = grid - combos;
+    p.ctas_group_a = a;
+    conv_halo_wgrad_kernel<<<grid, HALO_THREADS, smem, stream>>>(tmDY, tmX, p);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}

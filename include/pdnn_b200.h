@@ -63,6 +63,12 @@ int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout, int R, in
 int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
                               const pdnn_epilogue_t* epi, void* stream);
 
+/* Weight gradient of a 3x3 / stride 1 / pad 1 conv with halo reuse (csrc/conv_halo.cu): dw[Kout][3][3][C] fp32 +=
+ * (red.add, caller zero-fills). C in {64, 128}, Kout % 64 == 0, see pdnn_conv_halo_wgrad_supported(). */
+int pdnn_conv_halo_wgrad_supported(int batch, int H, int W, int C, int Kout, int R, int S, int pad);
+int pdnn_conv_halo_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout, float* dw,
+                              const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas, void* stream);
+
 /* Weight gradient of the same conv: dw[Kout][R][S][C] (fp32) += dy^T * im2col(x). out_mode must be 2.
  * ref: nn.Conv2d bwd-filter (same call sites). */
 int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout,

@@ -14,6 +14,7 @@ run the small-shape SIMT path (LeNet: N = 10/20/50, K = 25/500 do not form tenso
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -105,6 +106,8 @@ class Conv2d(Layer):
             self.halo_f = net.use_halo and net.device.type == "cuda" and F.conv_halo_supported(in_shape, cout, k, k, pad)
             self.halo_b = (not first) and net.use_halo and net.device.type == "cuda" and \
                 F.conv_halo_supported((n, h, w, cout), cin, k, k, pad)
+            self.halo_w = net.use_halo and net.device.type == "cuda" and os.environ.get("PDNN_NO_HALO_WGRAD") != "1" and \
+                F.conv_halo_wgrad_supported(in_shape, cout, k, k, pad)
         else:
             self.mode = "lowered"
         self.y = torch.empty(self.out_shape, device=dev, dtype=dt)
@@ -199,7 +202,10 @@ class Conv2d(Layer):
         dy2 = dy.view(m, self.cout)
         # ---- weight gradient first: the deepest parameters must leave for the master as early as possible
         if self.mode == "implicit":
-            F.conv_wgrad(x, dy, R=self.k, S=self.k, pad=self.pad, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
+            if self.halo_w:
+                F.conv_halo_wgrad(x, dy, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
+            else:
+                F.conv_wgrad(x, dy, R=self.k, S=self.k, pad=self.pad, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
         elif self.mode == "lowered":
             col = self._col(x, reuse=True)
             if self.kpad != self.kdim:

@@ -70,6 +70,8 @@ _SIGS = {
     "pdnn_conv_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_supported": [_I] * 8,
     "pdnn_conv_halo_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
+    "pdnn_conv_halo_wgrad_supported": [_I] * 8,
+    "pdnn_conv_halo_wgrad_bf16": [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P],
     "pdnn_conv_wgrad_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
     "pdnn_cast_f32_to_bf16": [_P, _P, _L, _P],
     "pdnn_cast_bf16_to_f32": [_P, _P, _L, _P],

@@ -96,6 +96,21 @@ def conv_halo_fprop(x, w, *, out=None, bias=None, relu=False, residual=None):
     return out
 
 
+def conv_halo_wgrad_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
+    n, h, w, c = x_shape
+    return bool(_lib.lib().pdnn_conv_halo_wgrad_supported(n, h, w, c, kout, R, S, pad))
+
+
+def conv_halo_wgrad(x, dy, out=None):
+    """dw[Kout,3,3,C] (fp32) += wgrad of a 3x3/s1/p1 conv through the halo-reuse kernel; out must be zero-filled."""
+    n, h, wd, c = x.shape
+    kout = dy.shape[-1]
+    if out is None:
+        out = torch.zeros(kout, 3, 3, c, device=x.device, dtype=F32)
+    call("pdnn_conv_halo_wgrad_bf16", x, dy, n, h, wd, c, kout, out, ptr(_GUARD[0]), ptr(_GUARD[1]), 0, stream_ptr())
+    return out
+
+
 def conv_wgrad(x, dy, *, R, S, pad, out=None, k_splits=0):
     """dw[Kout,R,S,C] (fp32) += dy^T * shifted(x); out must be zero-filled (or hold a running sum)."""
     n, h, wd, c = x.shape
