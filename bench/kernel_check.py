@@ -182,7 +182,9 @@ def conv_halo_diag():
 def conv_halo():
     F = _F()
     ok = True
-    for (n, h, c, k) in [(2, 32, 64, 64), (3, 16, 128, 128), (4, 16, 64, 128), (2, 32, 128, 64), (5, 8, 64, 64)]:
+    # the large-batch entries give every CTA many tiles (pipeline wrap-around, all issuer warps busy)
+    for (n, h, c, k) in [(2, 32, 64, 64), (3, 16, 128, 128), (4, 16, 64, 128), (2, 16, 128, 64), (5, 8, 64, 64), (600, 16, 64, 128),
+                         (160, 32, 64, 64), (400, 16, 128, 128)]:
         x = torch.randn(n, h, h, c, device="cuda").bfloat16()
         w = (torch.randn(k, 3, 3, c, device="cuda") / (3 * c ** 0.5)).bfloat16()
         bias = torch.randn(k, device="cuda")

@@ -58,8 +58,12 @@ constexpr int HALO_BN = 64;
 // With N = 64 one tcgen05.mma occupies the tensor pipe for ~32 cycles, but a single thread needs ~90 cycles to issue
 // one (descriptor moves into uniform registers; measured with ncu: tensor pipe 35% active, issuing warp 100% busy).
 // Three warps therefore issue for three different tiles at once, each into its own TMEM accumulator.
+// Every issuer owns a private slice of the stage ring (SI stages) and two private accumulators, so each mbarrier has
+// exactly one producer sequence and one consumer sequence in program order. (Sharing one ring / one accumulator pool
+// between issuers lets a fast issuer get two barrier phases ahead of a slow one; a parity wait cannot tell phase n
+// from phase n+2 -- found as a hang at batch 1024 with a 6-stage ring.)
 constexpr int HALO_ISSUERS = 3;
-constexpr int HALO_NACC = 4;
+constexpr int HALO_NACC = 6;
 
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const HaloParams p) {
@@ -99,7 +103,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         mbar_fence_init();
     }
     if (warp == 2) {
-        tmem_alloc(smem_u32(tmem_slot), HALO_NACC * HALO_BN);
+        tmem_alloc(smem_u32(tmem_slot), 512);      // 6 accumulators x 64 columns = 384 -> next power of two
         tmem_relinquish();
     }
     tc_fence_before();
@@ -120,22 +124,23 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             for (int tap = 0; tap < 9; ++tap)
                 for (int kb = 0; kb < p.KB; ++kb)
                     tma_load_2d(w_base + (tap * p.KB + kb) * 8192, &tmW, wbar, tap * p.C + kb * 64, cb * HALO_BN);
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb) {
+            const int SI = S / HALO_ISSUERS;           // stages per issuer
+            int seq = 0;
+            for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
                 const int n = tile / p.tiles_per_img;
                 const int p0 = (tile - n * p.tiles_per_img) * 128;
-                // first halo row: floor((p0 - Wp - 1) / Wp) in padded-flat rows == image row (p0-Wp-1)/Wp - 0; row r of the
-                // padded-flat space corresponds to image row r - 1 for the INPUT (one row of top padding)
                 int num = p0 - p.Wp - 1;
-                const int fl = num >= 0 ? num / p.Wp : -((-num + p.Wp - 1) / p.Wp);
-                const int h_lo = fl;            // input image row of the first box row, see kernel notes below
+                const int h_lo = num >= 0 ? num / p.Wp : -((-num + p.Wp - 1) / p.Wp);   // floor: first image row of the halo box
+                const int issuer = seq % HALO_ISSUERS;
+                const int t_i = seq / HALO_ISSUERS;
                 for (int kb = 0; kb < p.KB; ++kb) {
+                    const int m = t_i * p.KB + kb;                 // this issuer's unit counter
+                    const int stage = issuer * SI + (m % SI);
+                    const uint32_t phase = (uint32_t)(m / SI) & 1u;
                     mbar_wait(empty_bar(stage), phase ^ 1);
                     const uint32_t fb = full_bar(stage);
                     mbar_expect_tx(fb, (uint32_t)(p.Rb * p.Wp * 128));
                     tma_load_4d(a_base + stage * p.stage_bytes, &tmX, fb, kb * 64, -1, h_lo, n);
-                    if (++stage == S) { stage = 0; phase ^= 1; }
                 }
             }
         }
@@ -164,15 +169,17 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             // at index q + (r - 1 - h_lo) * Wp + (s - 1) of a halo box whose first row is image row h_lo = fl and whose
             // first column is w = -1.  origin = p0 - fl * Wp >= Wp + 1 keeps every index non-negative.
             const int origin = p0 - fl * p.Wp;
-            const int acc = seq % HALO_NACC;
-            const uint32_t acc_phase = (uint32_t)(seq / HALO_NACC) & 1u;
+            const int t_i = seq / HALO_ISSUERS;
+            const int acc = issuer * 2 + (t_i & 1);
+            const uint32_t acc_phase = (uint32_t)(t_i >> 1) & 1u;
             mbar_wait(tempty_bar(acc), acc_phase ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * HALO_BN;
+            const int SI = S / HALO_ISSUERS;
             for (int kb = 0; kb < p.KB; ++kb) {
-                const int unit = seq * p.KB + kb;
-                const int stage = unit % S;
-                const uint32_t phase = (uint32_t)(unit / S) & 1u;
+                const int m = t_i * p.KB + kb;
+                const int stage = issuer * SI + (m % SI);
+                const uint32_t phase = (uint32_t)(m / SI) & 1u;
                 mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
                 const uint32_t a_lo = (uint32_t)make_smem_desc_sw128(a_base + stage * p.stage_bytes + (uint32_t)origin * 128u, 16, 1024);
@@ -195,8 +202,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         const int ew = warp & 3;
         int seq = 0;
         for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
-            const int acc = seq % HALO_NACC;
-            const uint32_t acc_phase = (uint32_t)(seq / HALO_NACC) & 1u;
+            const int acc = (seq % HALO_ISSUERS) * 2 + ((seq / HALO_ISSUERS) & 1);
+            const uint32_t acc_phase = (uint32_t)((seq / HALO_ISSUERS) >> 1) & 1u;
             const int n = tile / p.tiles_per_img;
             const int q = (tile - n * p.tiles_per_img) * 128 + ew * 32 + lane;
             const int row = q / p.Wp;
@@ -253,7 +260,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, HALO_NACC * HALO_BN);
+        tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -274,7 +281,7 @@ extern "C" int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout
     const int stage_bytes = (Rb * Wp * 128 + 1023) / 1024 * 1024;
     const int w_bytes = 9 * (C / 64) * 8192;
     const int stages = (227 * 1024 - 2560 - w_bytes) / stage_bytes;
-    if (stages < 2) return 0;
+    if (stages < 3) return 0;          // one private stage per issuer warp at least
     if (W < 8 || H < 4) return 0;     // small maps waste most of a 128-position tile on padding: generic path is better
     return 1;
 }
@@ -295,7 +302,7 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     p.stage_bytes = (p.Rb * p.Wp * 128 + 1023) / 1024 * 1024;
     const int w_bytes = 9 * p.KB * 8192;
     p.stages = (227 * 1024 - 2560 - w_bytes) / p.stage_bytes;
-    if (p.stages > 6) p.stages = 6;
+    p.stages = p.stages >= 6 ? 6 : 3;   // a multiple of the issuer count: every issuer owns stages / 3 of the ring
     p.out = epi->out; p.ldo = epi->ldo; p.relu = epi->relu; p.bias = epi->bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
     p.guard_closed = epi->guard_closed; p.guard_step = epi->guard_step;
