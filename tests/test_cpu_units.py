@@ -183,3 +183,33 @@ def test_engine_layout_matches_torch_parameter_order_on_meta_device():
         assert spans[0][0] == 0 and spans[-1][1] == net.total
         assert all(spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1))
         assert net.buckets[0].end == net.total                      # bucket 0 = deepest layers, closes first
+
+
+def test_reference_import_paths_exist():
+    """The reference's module names stay importable (model_ops, nn_ops, datasets, mnist, cifar10, data_loader_ops,
+    distributed_functions, data_parallel_dist, the four role modules)."""
+    import importlib
+    for mod in ("model_ops.lenet", "model_ops.resnet", "model_ops.resnet_split", "model_ops.vgg", "nn_ops", "datasets", "mnist", "cifar10",
+                "data_loader_ops.my_data_loader", "distributed_functions.distributed_backward", "data_parallel_dist.data_parallel_dist",
+                "sync_replicas_master_nn", "sync_replicas_master_nn_normal", "distributed_worker", "distributed_worker_normal",
+                "distributed_nn", "single_machine", "evaluator", "comm_test"):
+        importlib.import_module("pytorch_distributed_nn_b200." + mod)
+    from pytorch_distributed_nn_b200.model_ops.resnet_split import ResNetSplit18, ResNetSplit50  # noqa: F401
+    from pytorch_distributed_nn_b200.sync_replicas_master_nn import GradientAccumulator, SyncReplicasMaster_NN  # noqa: F401
+    from pytorch_distributed_nn_b200.distributed_worker import DistributedWorker, ModelBuffer  # noqa: F401
+    from pytorch_distributed_nn_b200.distributed_functions.distributed_backward import backward
+    import torch
+    x = torch.ones(3, requires_grad=True)
+    backward([(x * 2).sum()])
+    assert torch.equal(x.grad, torch.full((3,), 2.0))
+
+
+def test_ddp_comparator_single_process_is_identity():
+    import torch
+    from pytorch_distributed_nn_b200.data_parallel_dist import DistributedDataParallel
+    from pytorch_distributed_nn_b200.models import build_model
+    net = DistributedDataParallel(build_model("LeNet"))
+    out = net(torch.randn(2, 1, 28, 28))
+    out.sum().backward()
+    net.finish_backward()
+    assert len(net.buckets) >= 1 and all(p.grad is not None for p in net.module.parameters())
