@@ -241,6 +241,8 @@ class SyncReplicasMaster_NN(NN_Trainer):
                     self.cur_step = i + getattr(self, "step_offset", 0)
                     self.save_checkpoint()
         torch.cuda.synchronize()
+        if self._pending_ckpt is not None:
+            self._pending_ckpt.join()
         self.cur_step = ps.step
         self.summary = timer.summary()
         self.logger.log(event="summary", **self.summary)
