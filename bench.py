@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--grad-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--inject-delay", default="", help="straggler spec, e.g. 'const:ranks=1,2,3:ms=5' (see parallel/delays.py)")
     ap.add_argument("--n-buckets", type=int, default=8)
+    ap.add_argument("--cuda-graph", action="store_true", help="replay the whole step from a CUDA graph (launch-bound small batches)")
     ap.add_argument("--master-only", action="store_true", help="rank 0 is master-only as in the reference (n = N-1 workers)")
     ap.add_argument("--interval-ms", type=float, default=0.0, help="interval policy: the master closes each step after this deadline")
     ap.add_argument("--worker-times-cdf", action="store_true", help="report the per-(worker, step) time distribution (TF study)")
@@ -172,6 +173,9 @@ def main():
         return losses
 
     # ---- warm-up (untimed) -------------------------------------------------------------------
+    run_resident(2)
+    if args.cuda_graph:
+        ps.enable_cuda_graph(dev_x[0], dev_y[0])
     run_resident(args.warmup)
     run_e2e(max(1, min(args.warmup, 3)))
     sync_all()
@@ -244,7 +248,7 @@ def main():
                        "parallelism": (f"ps-dp{ps.n_workers} (master+worker colocated on GPU0, k={ps.k} of n={ps.n_workers})" if ps.colocate else
                                        f"ps-dp{ps.n_workers} (GPU0 master-only as in the reference, k={ps.k} of n={ps.n_workers})"),
                        "optimizer": f"momentum-SGD lr={args.lr} mu={args.momentum} (fp32 master weights)",
-                       "grad_wire_dtype": args.grad_dtype, "inject_delay": args.inject_delay or "none",
+                       "grad_wire_dtype": args.grad_dtype, "cuda_graph": bool(args.cuda_graph), "inject_delay": args.inject_delay or "none",
                        "l2_policy": "working set (activations >> 126 MB L2 at batch 1024; 4 input batches rotate) exceeds L2"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/sec", "ms_per_step": round(e2e_ms / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "final_loss": losses[-1]},

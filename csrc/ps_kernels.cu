@@ -26,7 +26,8 @@ enum { CTL_MASK = 0, CTL_MASK_STEP = 1, CTL_DONE = 2, CTL_NSEL = 3, CTL_ERR = 4,
 __global__ void __launch_bounds__(512) ps_push_kernel(const float* __restrict__ grad, void* __restrict__ slot, long long n,
                                                       int slot_is_bf16, uint32_t* flag_peer, uint32_t step,
                                                       uint32_t* local_counter, const uint32_t* guard_closed,
-                                                      const uint32_t* guard_step) {
+                                                      const uint32_t* guard_step, const uint32_t* step_ptr) {
+    if (step_ptr != nullptr) step = ld_relaxed_sys(step_ptr);   // CUDA-graph mode: the step number lives on the device
     if (guard_closed != nullptr) {   // a killed worker drops its contribution (CTA-uniform decision)
         __shared__ int s_abort;
         if (threadIdx.x == 0) s_abort = ld_relaxed_sys(guard_closed) >= ld_relaxed_sys(guard_step);
@@ -82,6 +83,8 @@ __device__ __forceinline__ void multimem_st_v4(void* mc_addr, uint4 v) {
 
 __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_constant__ MasterArgs margs) {
     const pdnn_ps_master_t& a = margs.a;
+    // CUDA-graph mode: the step to close is read from device memory (and advanced by the last block below)
+    const uint32_t cur_step = a.step_ptr != nullptr ? ld_relaxed_sys(a.step_ptr) : a.step;
     __shared__ uint32_t s_mask;
     __shared__ uint32_t s_nsel;
     uint32_t* ctl = a.control;
@@ -94,7 +97,7 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
             const uint32_t want = (uint32_t)a.k;
             for (;;) {
                 for (int w = 0; w < a.n_workers && count < want; ++w) {
-                    if (!(mask & (1u << w)) && ld_acquire_sys(a.arrival_flags + w) == a.step) {
+                    if (!(mask & (1u << w)) && ld_acquire_sys(a.arrival_flags + w) == cur_step) {
                         mask |= 1u << w;
                         ++count;
                     }
@@ -110,7 +113,7 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
             for (int w = 0; w < a.n_workers; ++w) {
                 if (!(mask & (1u << w))) {
                     kill |= 1u << w;
-                    if (a.worker_closed[w] != nullptr) st_release_sys(a.worker_closed[w], a.step);
+                    if (a.worker_closed[w] != nullptr) st_release_sys(a.worker_closed[w], cur_step);
                 }
             }
             ctl[CTL_NSEL] = count;
@@ -118,14 +121,14 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
             margs.result[0] = mask;
             margs.result[1] = kill;
             margs.result[2] = count;
-            margs.result[3] = err ? 0xDEADu : a.step;
+            margs.result[3] = err ? 0xDEADu : cur_step;
             ctl[CTL_MASK] = mask;
             __threadfence();
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ctl + CTL_MASK_STEP), "r"(a.step) : "memory");
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ctl + CTL_MASK_STEP), "r"(cur_step) : "memory");
             s_mask = mask;
             s_nsel = count;
         } else {
-            while (ld_acquire_gpu(ctl + CTL_MASK_STEP) != a.step) __nanosleep(100);
+            while (ld_acquire_gpu(ctl + CTL_MASK_STEP) != cur_step) __nanosleep(100);
             s_mask = ctl[CTL_MASK];
             s_nsel = ctl[CTL_NSEL];
         }
@@ -228,9 +231,10 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
         const uint32_t done = atom_add_acqrel_gpu(ctl + CTL_DONE, 1u) + 1u;
         if (done == gridDim.x) {
             ctl[CTL_DONE] = 0;
+            if (a.step_ptr != nullptr) st_relaxed_sys(a.step_ptr, cur_step + 1u);
             __threadfence_system();
             for (int w = 0; w < a.n_workers; ++w)
-                if (a.worker_ready[w] != nullptr) st_release_sys(a.worker_ready[w], a.step + 1u);
+                if (a.worker_ready[w] != nullptr) st_release_sys(a.worker_ready[w], cur_step + 1u);
         }
     }
 }
@@ -245,6 +249,17 @@ __global__ void ps_wait_flag_kernel(const uint32_t* flag, uint32_t value, uint32
     }
     if (cur_step_word != nullptr) st_release_sys(cur_step_word, ok ? value : 0xFFFFFFFFu);
     if (status != nullptr) *status = ok;
+}
+
+// CUDA-graph mode: advance the device-side step word and wait for that step's weights.
+__global__ void ps_wait_next_kernel(const uint32_t* flag, uint32_t* step_word, long long timeout_ns) {
+    const uint32_t want = ld_relaxed_sys(step_word) + 1u;
+    const uint64_t t0 = globaltimer_ns();
+    while (ld_acquire_sys(flag) < want) {
+        if (timeout_ns > 0 && globaltimer_ns() - t0 > (uint64_t)timeout_ns) break;
+        __nanosleep(100);
+    }
+    st_release_sys(step_word, want);
 }
 
 __global__ void ps_delay_kernel(long long ns, const uint32_t* guard_closed, const uint32_t* guard_step) {
@@ -307,7 +322,22 @@ extern "C" int pdnn_ps_push(const float* grad, void* slot_peer, long long n, int
     uint32_t* counter = nullptr;
     if (int rc = push_counter(&counter)) return rc;
     const int grid = ps_grid(n / 8 + 1, 512, max_ctas);
-    ps_push_kernel<<<grid, 512, 0, ST(stream)>>>(grad, slot_peer, n, slot_is_bf16, flag_peer, step, counter, guard_closed, guard_step);
+    ps_push_kernel<<<grid, 512, 0, ST(stream)>>>(grad, slot_peer, n, slot_is_bf16, flag_peer, step, counter, guard_closed, guard_step, nullptr);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+// Same push, but the step tag is read from device memory when the kernel runs: nothing in the launch depends on the
+// step number, so the launch can be replayed from a CUDA graph.
+extern "C" int pdnn_ps_push_dev(const float* grad, void* slot_peer, long long n, int slot_is_bf16, uint32_t* flag_peer,
+                                const uint32_t* step_ptr, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
+                                void* stream) {
+    PDNN_REQUIRE(n > 0 && step_ptr != nullptr, "ps_push_dev: empty bucket or missing step word");
+    uint32_t* counter = nullptr;
+    if (int rc = push_counter(&counter)) return rc;
+    const int grid = ps_grid(n / 8 + 1, 512, max_ctas);
+    ps_push_kernel<<<grid, 512, 0, ST(stream)>>>(grad, slot_peer, n, slot_is_bf16, flag_peer, 0u, counter, guard_closed, guard_step, step_ptr);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
@@ -332,6 +362,13 @@ extern "C" int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* resul
 
 extern "C" int pdnn_ps_wait_flag(const uint32_t* flag, uint32_t value, uint32_t* cur_step_word, long long timeout_ns, void* stream) {
     ps_wait_flag_kernel<<<1, 1, 0, ST(stream)>>>(flag, value, cur_step_word, timeout_ns, nullptr);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pdnn_ps_wait_next(const uint32_t* flag, uint32_t* step_word, long long timeout_ns, void* stream) {
+    ps_wait_next_kernel<<<1, 1, 0, ST(stream)>>>(flag, step_word, timeout_ns);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -194,6 +194,8 @@ typedef struct pdnn_ps_master {
     uint32_t step;                           /* step being closed; workers are released with step+1 */
     long long deadline_ns;                   /* >0: interval policy, close with whatever arrived */
     int max_ctas;
+    uint32_t* step_ptr;                      /* non-NULL: read `step` from this device word and advance it at the end, so
+                                                that the launch does not depend on the step number (CUDA-graph replay) */
 } pdnn_ps_master_t;
 
 /* Master: wait for the first k arrivals of `step`, publish the kill mask to the late workers
@@ -208,6 +210,12 @@ int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* st
 /* Worker: block the stream until *ready_flag >= step (ref: distributed_worker.py:202-208 irecv tag 10). */
 int pdnn_ps_wait_flag(const uint32_t* flag, uint32_t value, uint32_t* cur_step_word, long long timeout_ns,
                       void* stream);
+/* Step-number-free forms for CUDA-graph replay: the push reads its step tag from *step_ptr; wait_next advances
+ * *step_word by one and waits until *flag reaches it. */
+int pdnn_ps_push_dev(const float* grad, void* slot_peer, long long n, int slot_is_bf16, uint32_t* flag_peer,
+                     const uint32_t* step_ptr, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
+                     void* stream);
+int pdnn_ps_wait_next(const uint32_t* flag, uint32_t* step_word, long long timeout_ns, void* stream);
 /* Device-side straggler injection: busy-wait `ns` nanoseconds on %globaltimer (aborts early when the
  * guard closes). ref: pure_py_code/distributed_worker.py:130-132 (time.sleep(0.5) per layer). */
 int pdnn_delay(long long ns, const uint32_t* guard_closed, const uint32_t* guard_step, void* stream);

@@ -37,7 +37,7 @@ class PSMaster(C.Structure):
         ("master_w", C.c_void_p), ("momentum", C.c_void_p), ("control", C.c_void_p),
         ("n", C.c_longlong), ("n_workers", C.c_int), ("k", C.c_int), ("slot_is_bf16", C.c_int),
         ("weights_are_bf16", C.c_int), ("avg_mode", C.c_int), ("lr", C.c_float), ("mu", C.c_float),
-        ("step", C.c_uint32), ("deadline_ns", C.c_longlong), ("max_ctas", C.c_int),
+        ("step", C.c_uint32), ("deadline_ns", C.c_longlong), ("max_ctas", C.c_int), ("step_ptr", C.c_void_p),
     ]
 
 
@@ -110,6 +110,8 @@ _SIGS = {
     "pdnn_sigmoid_bwd_f32": [_P, _P, _P, _L, _P],
     "pdnn_gemm_simt_f32": [_P, _I, _L, _P, _I, _L, _P, _L, _I, _I, _I, _F, _P, _I, _I, _P],
     "pdnn_ps_push": [_P, _P, _L, _I, _P, _U, _P, _P, _I, _P],
+    "pdnn_ps_push_dev": [_P, _P, _L, _I, _P, _P, _P, _P, _I, _P],
+    "pdnn_ps_wait_next": [_P, _P, _L, _P],
     "pdnn_ps_master_step": [C.POINTER(PSMaster), _P, _P],
     "pdnn_ps_wait_flag": [_P, _U, _P, _L, _P],
     "pdnn_delay": [_L, _P, _P, _P],

@@ -36,7 +36,7 @@ from .protocol import AVG_MODES, STEP_START_
 U32 = 4
 FLAG_WORDS = 256          # per-rank flag block (uint32 words)
 W_READY, W_CLOSED, W_STEP = 0, 1, 2         # worker-side words
-M_ARRIVAL, M_CONTROL, M_RESULT = 32, 64, 128  # master-side words (arrival[n], control[64], result[4])
+M_ARRIVAL, M_CONTROL, M_RESULT, M_STEPW = 32, 64, 128, 160  # master-side words (arrival[n], control[64], result[4], step)
 
 
 class B200ParameterServer:
@@ -64,6 +64,8 @@ class B200ParameterServer:
         self.delay_fn = delay_fn
         self.step = STEP_START_
         self.batch_size = batch_size
+        self._graph_mode = False
+        self._graph = None
 
         # ---- network (every rank builds it: the master needs the layout, workers need the layers)
         self.net: Network = self._build(network, batch_size, n_buckets, group)
@@ -127,9 +129,14 @@ class B200ParameterServer:
 
             def on_bucket(b):
                 flag = self._arrival_ptr if b.index == last_bucket else None
-                _lib.call("pdnn_ps_push", net.g.data_ptr() + b.start * 4, self._slot_ptr + b.start * self.slot_elem,
-                          b.end - b.start, int(self.grad_bf16), flag, self.step,
-                          self.closed_word.data_ptr(), self.step_word.data_ptr(), 0, _lib.stream_ptr())
+                if self._graph_mode:      # step tag read from the device word: the launch is replayable
+                    _lib.call("pdnn_ps_push_dev", net.g.data_ptr() + b.start * 4, self._slot_ptr + b.start * self.slot_elem,
+                              b.end - b.start, int(self.grad_bf16), flag, self.step_word.data_ptr(),
+                              self.closed_word.data_ptr(), self.step_word.data_ptr(), 0, _lib.stream_ptr())
+                else:
+                    _lib.call("pdnn_ps_push", net.g.data_ptr() + b.start * 4, self._slot_ptr + b.start * self.slot_elem,
+                              b.end - b.start, int(self.grad_bf16), flag, self.step,
+                              self.closed_word.data_ptr(), self.step_word.data_ptr(), 0, _lib.stream_ptr())
 
             net.on_bucket = on_bucket
         if self.is_master:
@@ -186,7 +193,10 @@ class B200ParameterServer:
         """Enqueue one worker step (no host synchronisation). Returns the device loss tensor."""
         net = self.net
         st = _lib.stream_ptr()
-        _lib.call("pdnn_ps_wait_flag", self.flags.data_ptr() + W_READY * U32, self.step, self.step_word.data_ptr(), 0, st)
+        if self._graph_mode:
+            _lib.call("pdnn_ps_wait_next", self.flags.data_ptr() + W_READY * U32, self.step_word.data_ptr(), 0, st)
+        else:
+            _lib.call("pdnn_ps_wait_flag", self.flags.data_ptr() + W_READY * U32, self.step, self.step_word.data_ptr(), 0, st)
         F.set_abort_guard(self.closed_word, self.step_word)
         try:
             net.prepare()
@@ -203,10 +213,58 @@ class B200ParameterServer:
         """Enqueue the master's aggregate/update/broadcast kernel for the current step."""
         m = self._margs
         m.step = self.step
+        m.step_ptr = self._flag_ptr(0, M_STEPW) if self._graph_mode else None
         _lib.call("pdnn_ps_master_step", C.byref(m), self.result.data_ptr(), _lib.stream_ptr())
+
+    def enable_cuda_graph(self, x_example=None, y_example=None):
+        """Capture one complete step of this rank (wait -> layouts -> forward -> loss -> backward with bucket pushes ->
+        [master kernel]) into a CUDA graph; later ``train_step`` calls copy the batch into static buffers and replay.
+        The step number moves to device words (`pdnn_ps_wait_next`, `pdnn_ps_push_dev`, master ``step_ptr``) so nothing in
+        the captured launches depends on it. Call on EVERY rank at the same step (one real step runs as warm-up).
+        Host-computed per-step delays (``delay_fn``) cannot be replayed and are rejected."""
+        if self.delay_fn is not None:
+            raise ValueError("CUDA-graph replay is incompatible with host-scheduled delay injection")
+        torch.cuda.synchronize()
+        dev = self.device
+        if self.is_worker:
+            self.flags[W_STEP] = self.step - 1         # last completed step; wait_next advances it
+        if self.is_master:
+            self.flags[M_STEPW] = self.step
+        self._graph_mode = True
+        if self.is_worker:
+            self._gx = x_example.clone()
+            self._gy = y_example.clone()
+        else:
+            self._gx = self._gy = None
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):                  # one eager step in graph mode (also the warm-up torch asks for)
+            self._step_body(self._gx, self._gy)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize()
+        self.step += 1
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._graph_loss = self._step_body(self._gx, self._gy)
+        return self
+
+    def _step_body(self, x, y):
+        loss = None
+        if self.is_worker:
+            loss = self.worker_step(x, y)
+        if self.is_master:
+            self.master_step()
+        return loss
 
     def train_step(self, x_nchw_f32=None, labels=None):
         """One synchronous-SGD step of this rank's role(s); advances the step counter."""
+        if self._graph is not None:
+            if self.is_worker:
+                self._gx.copy_(x_nchw_f32, non_blocking=True)
+                self._gy.copy_(labels, non_blocking=True)
+            self._graph.replay()
+            self.step += 1
+            return self._graph_loss
         loss = None
         if self.is_worker:
             loss = self.worker_step(x_nchw_f32, labels)
