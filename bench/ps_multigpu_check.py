@@ -32,7 +32,7 @@ def gather_vec(t, world):
     return out
 
 
-def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colocate):
+def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colocate, graph=False):
     dev = torch.device("cuda", torch.cuda.current_device())
     delay_fn = parse_delay_spec(delay_spec) if delay_spec else None
     lr, mu = 0.05, 0.5
@@ -52,8 +52,12 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
     ok = True
     log = []
     for s in range(1, steps + 1):
+        if graph and s == 2:
+            # from step 2 on the whole step is replayed from a CUDA graph; the capture itself runs step 2 for real
+            ps.enable_cuda_graph(x, y)
+        else:
+            ps.train_step(x, y)
         # no host synchronisation inside the step: the master kernel polls while the workers are still computing
-        ps.train_step(x, y)
         torch.cuda.synchronize()
         dist.barrier()
         # what each worker produced this step (a killed worker's gradient is partial garbage, never used)
@@ -123,6 +127,7 @@ def main():
     results = {}
     results["all_n_colocated_fp32"] = run_case(args.network, args.batch, rank, world, args.steps, None, "", "fp32", True)
     results["all_n_colocated_bf16"] = run_case(args.network, args.batch, rank, world, args.steps, None, "", "bf16", True)
+    results["all_n_colocated_cuda_graph"] = run_case(args.network, args.batch, rank, world, args.steps + 1, None, "", "fp32", True, graph=True)
     n_workers = world
     if n_workers >= 2:
         # the last worker is delayed by 30 ms on the device; k = n-1

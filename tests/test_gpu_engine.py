@@ -205,26 +205,24 @@ def test_multi_gpu_parameter_server_checks():
 
 
 def test_cuda_graph_replay_matches_eager_steps():
-    """Same init, same batches: 5 eager steps vs 2 eager + graph-replayed steps give the same master weights."""
+    """Same init, same batches: 5 eager steps vs 2 eager + 1 capture warm-up + 2 graph-replayed steps give the same master
+    weights (LeNet: fp32 path, so the only run-to-run difference is the order of split-K atomics)."""
     from pytorch_distributed_nn_b200.parallel.b200_ps import B200ParameterServer
-    x = [torch.empty(32, 3, 32, 32, device="cuda").uniform_(0, 255) for _ in range(5)]
+    x = [torch.randn(32, 1, 28, 28, device="cuda") for _ in range(5)]
     y = [torch.randint(0, 10, (32,), device="cuda") for _ in range(5)]
-    a = B200ParameterServer("ResNet18", 32, 0, 1, lr=0.05, momentum=0.5, seed=3, grad_dtype="fp32")
+    a = B200ParameterServer("LeNet", 32, 0, 1, lr=0.05, momentum=0.5, seed=3, grad_dtype="fp32")
     for i in range(5):
         a.train_step(x[i], y[i])
     torch.cuda.synchronize()
     wa = a.net.w32.clone()
     a.close()
-    b = B200ParameterServer("ResNet18", 32, 0, 1, lr=0.05, momentum=0.5, seed=3, grad_dtype="fp32")
+    b = B200ParameterServer("LeNet", 32, 0, 1, lr=0.05, momentum=0.5, seed=3, grad_dtype="fp32")
     b.train_step(x[0], y[0])
     b.train_step(x[1], y[1])
-    b._gx_src = None
-    # the capture runs one real step on its example batch (step 3), then two replays
-    b.enable_cuda_graph(x[2], y[2])
+    b.enable_cuda_graph(x[2], y[2])        # runs one real step on its example batch (step 3) and captures
     b.train_step(x[3], y[3])
     loss = b.train_step(x[4], y[4])
     torch.cuda.synchronize()
     assert b.last_result() == (1, 0, 1, 5) and float(loss) == float(loss)
-    # split-K red.add ordering differs run to run: compare with a tolerance, not bitwise
-    assert torch.allclose(b.net.w32, wa, rtol=2e-2, atol=2e-3)
+    assert torch.allclose(b.net.w32, wa, rtol=1e-4, atol=1e-5)
     b.close()
