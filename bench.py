@@ -42,7 +42,8 @@ def parse():
     ap.add_argument("--grad-dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--inject-delay", default="", help="straggler spec, e.g. 'const:ranks=1,2,3:ms=5' (see parallel/delays.py)")
     ap.add_argument("--n-buckets", type=int, default=8)
-    ap.add_argument("--cuda-graph", action="store_true", help="replay the whole step from a CUDA graph (launch-bound small batches)")
+    ap.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false", default=True,
+                    help="enqueue every kernel of every step from the host instead of replaying the step from a CUDA graph")
     ap.add_argument("--master-only", action="store_true", help="rank 0 is master-only as in the reference (n = N-1 workers)")
     ap.add_argument("--interval-ms", type=float, default=0.0, help="interval policy: the master closes each step after this deadline")
     ap.add_argument("--worker-times-cdf", action="store_true", help="report the per-(worker, step) time distribution (TF study)")
@@ -174,8 +175,11 @@ def main():
 
     # ---- warm-up (untimed) -------------------------------------------------------------------
     run_resident(2)
-    if args.cuda_graph:
+    if args.cuda_graph and delay_fn is None:
+        # the whole step (wait, forward, loss, backward + bucket pushes, master kernel) becomes one graph launch
         ps.enable_cuda_graph(dev_x[0], dev_y[0])
+    else:
+        args.cuda_graph = False
     run_resident(args.warmup)
     run_e2e(max(1, min(args.warmup, 3)))
     sync_all()
