@@ -342,6 +342,13 @@ def batchnorm():
         ok &= report(f"bn_bwd_dres[{c}]", rel_err(dres, rr.grad.permute(0, 2, 3, 1)), 3e-2)
         ok &= report(f"bn_bwd_dgamma[{c}]", rel_err(dg, g.grad), 2e-2)
         ok &= report(f"bn_bwd_dbeta[{c}]", rel_err(db, b.grad), 2e-2)
+        # no-residual form: the ReLU mask is rebuilt from x (y = None)
+        y2, mi2 = F.bn_forward(x, gamma, beta, relu=True)
+        xr2 = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+        yr2 = torch.relu(torch.nn.functional.batch_norm(xr2, None, None, gamma, beta, training=True))
+        yr2.backward(dy.float().permute(0, 3, 1, 2))
+        dx2, _, dg2, db2 = F.bn_backward(x, None, dy, gamma, mi2, relu=True, beta=beta)
+        ok &= report(f"bn_bwd_maskx_dx[{c}]", rel_err(dx2, xr2.grad.permute(0, 2, 3, 1)), 3e-2)
     return ok
 
 

@@ -307,4 +307,21 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+// Column sums across the 32 lanes of a warp for 32 columns held one-per-register: after the call lane L holds the sum
+// of column L over all lanes (31 shuffles: each round halves the number of live registers). Used by the conv epilogues
+// to produce BatchNorm statistics without a second pass over the activation.
+__device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool hi = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = hi ? v[i] : v[i + off];
+            const float keep = hi ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
 }  // namespace pdnn

@@ -37,6 +37,7 @@ struct HaloParams {
     const uint32_t* guard_closed;
     const uint32_t* guard_step;
     int use_base_offset;
+    float* bn_stats;     // optional [2][Kout]: per-channel sum and sum of squares of the (bf16-rounded) output
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr, int use_base_offset) {
@@ -201,6 +202,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     } else if (warp >= 4) {
         const int ew = warp & 3;
         int seq = 0;
+        // BatchNorm statistics of the output, accumulated per lane across all tiles of this CTA (the CTA's 64 output
+        // channels never change), flushed with one atomicAdd per lane and 32-column chunk at the very end
+        float st_sum[HALO_BN / 32] = {0.f, 0.f}, st_sq[HALO_BN / 32] = {0.f, 0.f};
         for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
             const int acc = (seq % HALO_ISSUERS) * 2 + ((seq / HALO_ISSUERS) & 1);
             const uint32_t acc_phase = (uint32_t)((seq / HALO_ISSUERS) >> 1) & 1u;
@@ -212,48 +216,68 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             const long long pix = ((long long)n * p.H + row) * p.W + (colp - 1);
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
-#pragma unroll 1
+#pragma unroll
             for (int c = 0; c < HALO_BN / 32; ++c) {
                 uint32_t v[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(ew * 32) << 16) + acc * HALO_BN + c * 32, v);
                 tmem_ld_wait();
-                if (!valid) continue;
                 const int col0 = cb * HALO_BN + c * 32;
                 float f[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-                if (p.bias != nullptr) {
+                if (valid) {
+                    if (p.bias != nullptr) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + col0 + i);
-                }
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.ldo + col0;
-                if (p.residual != nullptr) {
-                    const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.ldo + col0);
+                        for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + col0 + i);
+                    }
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.ldo + col0;
+                    if (p.residual != nullptr) {
+                        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.ldo + col0);
+#pragma unroll
+                        for (int q4 = 0; q4 < 4; ++q4) {
+                            const uint4 u = rp[q4];
+                            float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+                            f[q4 * 8 + 0] += a.x; f[q4 * 8 + 1] += a.y; f[q4 * 8 + 2] += b.x; f[q4 * 8 + 3] += b.y;
+                            f[q4 * 8 + 4] += cc.x; f[q4 * 8 + 5] += cc.y; f[q4 * 8 + 6] += d.x; f[q4 * 8 + 7] += d.y;
+                        }
+                    }
+                    if (p.relu) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+                    }
 #pragma unroll
                     for (int q4 = 0; q4 < 4; ++q4) {
-                        const uint4 u = rp[q4];
-                        float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-                        f[q4 * 8 + 0] += a.x; f[q4 * 8 + 1] += a.y; f[q4 * 8 + 2] += b.x; f[q4 * 8 + 3] += b.y;
-                        f[q4 * 8 + 4] += cc.x; f[q4 * 8 + 5] += cc.y; f[q4 * 8 + 6] += d.x; f[q4 * 8 + 7] += d.y;
+                        uint4 w;
+                        w.x = pack_bf16x2(f[q4 * 8 + 0], f[q4 * 8 + 1]);
+                        w.y = pack_bf16x2(f[q4 * 8 + 2], f[q4 * 8 + 3]);
+                        w.z = pack_bf16x2(f[q4 * 8 + 4], f[q4 * 8 + 5]);
+                        w.w = pack_bf16x2(f[q4 * 8 + 6], f[q4 * 8 + 7]);
+                        *reinterpret_cast<uint4*>(o + q4 * 8) = w;
                     }
                 }
-                if (p.relu) {
+                if (p.bn_stats != nullptr) {
+                    // statistics of exactly what was stored (bf16-rounded); positions on the padding columns count as 0
+                    float s1[32], s2[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
-                }
-#pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4) {
-                    uint4 w;
-                    w.x = pack_bf16x2(f[q4 * 8 + 0], f[q4 * 8 + 1]);
-                    w.y = pack_bf16x2(f[q4 * 8 + 2], f[q4 * 8 + 3]);
-                    w.z = pack_bf16x2(f[q4 * 8 + 4], f[q4 * 8 + 5]);
-                    w.w = pack_bf16x2(f[q4 * 8 + 6], f[q4 * 8 + 7]);
-                    *reinterpret_cast<uint4*>(o + q4 * 8) = w;
+                    for (int i = 0; i < 32; ++i) {
+                        const float r = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
+                        s1[i] = r;
+                        s2[i] = r * r;
+                    }
+                    st_sum[c] += warp_column_sums(s1, lane);
+                    st_sq[c] += warp_column_sums(s2, lane);
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+        if (p.bn_stats != nullptr) {
+#pragma unroll
+            for (int c = 0; c < HALO_BN / 32; ++c) {
+                atomicAdd(p.bn_stats + cb * HALO_BN + c * 32 + lane, st_sum[c]);
+                atomicAdd(p.bn_stats + p.Kout + cb * HALO_BN + c * 32 + lane, st_sq[c]);
+            }
         }
     }
     tc_fence_before();
@@ -286,8 +310,8 @@ extern "C" int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout
     return 1;
 }
 
-extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
-                                         const pdnn_epilogue_t* epi, void* stream_) {
+static int conv_halo_fprop_impl(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                const pdnn_epilogue_t* epi, float* bn_stats, void* stream_) {
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     PDNN_REQUIRE(pdnn_conv_halo_supported(batch, H, W, C, Kout, 3, 3, 1), "conv_halo: unsupported geometry (C=%d Kout=%d %dx%d)", C, Kout, H, W);
     PDNN_REQUIRE(epi != nullptr && epi->out != nullptr && epi->out_mode == 0, "conv_halo: bf16 output required");
@@ -306,6 +330,7 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     p.out = epi->out; p.ldo = epi->ldo; p.relu = epi->relu; p.bias = epi->bias;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
     p.guard_closed = epi->guard_closed; p.guard_step = epi->guard_step;
+    p.bn_stats = bn_stats;
     {
         const char* e = getenv("PDNN_HALO_BASE_OFFSET");
         p.use_base_offset = e != nullptr ? atoi(e) : 0;
@@ -343,6 +368,19 @@ extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int bat
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
+}
+
+extern "C" int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                         const pdnn_epilogue_t* epi, void* stream) {
+    return conv_halo_fprop_impl(x, wgt, batch, H, W, C, Kout, epi, nullptr, stream);
+}
+
+// Same convolution; additionally adds the per-output-channel sum and sum of squares of the stored (bf16) output into
+// bn_stats[0][k] / bn_stats[1][k] (fp32, caller zero-fills): the statistics pass of the BatchNorm that follows.
+extern "C" int pdnn_conv_halo_fprop_stats_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                               const pdnn_epilogue_t* epi, float* bn_stats, void* stream) {
+    PDNN_REQUIRE(bn_stats != nullptr, "conv_halo_fprop_stats: bn_stats is NULL");
+    return conv_halo_fprop_impl(x, wgt, batch, H, W, C, Kout, epi, bn_stats, stream);
 }
 
 // =================================================================================================================

@@ -245,7 +245,8 @@ __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, in
 template <int MODE>   // 0: stats of x ; 1: backward sums (dz, dz*xhat)
 __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
                                                         const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
-                                                        float* __restrict__ out, long long M, int C, int relu) {
+                                                        float* __restrict__ out, long long M, int C, int relu,
+                                                        const float* __restrict__ gamma, const float* __restrict__ beta) {
     extern __shared__ float sh[];   // [2][rows_per_iter][C]
     const int tpr = C / 8;                        // threads per row (<= 256)
     const int rpi = max(1, (int)blockDim.x / tpr); // rows per iteration
@@ -256,10 +257,16 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
         float a0[8], a1[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
-        float mean[8], inv[8];
+        float mean[8], inv[8], sc[8], sf[8];
+        // without a residual the ReLU mask is a function of x alone (y > 0 <=> gamma*xhat + beta > 0): y is not read
+        const bool mask_from_x = (MODE == 1) && relu && (y == nullptr);
         if (MODE == 1) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { mean[j] = mean_invstd[ct * 8 + j]; inv[j] = mean_invstd[C + ct * 8 + j]; }
+            for (int j = 0; j < 8; ++j) {
+                mean[j] = mean_invstd[ct * 8 + j]; inv[j] = mean_invstd[C + ct * 8 + j];
+                sc[j] = 0.f; sf[j] = 0.f;
+                if (mask_from_x) { sc[j] = gamma[ct * 8 + j] * inv[j]; sf[j] = beta[ct * 8 + j] - mean[j] * sc[j]; }
+            }
         }
         for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += (long long)gridDim.x * rpi) {
             const long long off = row * C + ct * 8;
@@ -271,7 +278,10 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
             } else {
                 float dv[8];
                 load8(dy + off, dv);
-                if (relu) {
+                if (mask_from_x) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (!(xv[j] * sc[j] + sf[j] > 0.f)) dv[j] = 0.f;
+                } else if (relu) {
                     float yv[8];
                     load8(y + off, yv);
 #pragma unroll
@@ -352,7 +362,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
                                                            const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ sums,
                                                            __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
-                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu) {
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu,
+                                                           const float* __restrict__ beta) {
     const int tpr = C / 8;
     const int rpi = max(1, (int)blockDim.x / tpr);
     const int ct = threadIdx.x % tpr;
@@ -360,13 +371,15 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
     if (rgrp >= rpi) return;
     const float invM = 1.f / (float)M;
     // dx = a*dz + b*x + c0 with a = gamma*inv, b = -a*inv*s1/M, c0 = -a*s0/M - b*mean
-    float ka[8], kb[8], kc[8];
+    float ka[8], kb[8], kc[8], sf[8];
+    const bool mask_from_x = relu && (y == nullptr);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const int c = ct * 8 + j;
         const float mean = mean_invstd[c], inv = mean_invstd[C + c];
         const float s0 = sums[c], s1 = sums[C + c];
         ka[j] = gamma[c] * inv;
+        sf[j] = mask_from_x ? beta[c] - mean * ka[j] : 0.f;
         kb[j] = -ka[j] * inv * s1 * invM;
         kc[j] = -ka[j] * s0 * invM - kb[j] * mean;
         if (blockIdx.x == 0 && rgrp == 0) { dgamma[c] = s1; dbeta[c] = s0; }
@@ -377,7 +390,10 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
         float xv[8], dv[8];
         load8(x + off, xv);
         load8(dy + off, dv);
-        if (relu) {
+        if (mask_from_x) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (!(xv[j] * ka[j] + sf[j] > 0.f)) dv[j] = 0.f;
+        } else if (relu) {
             float yv[8];
             load8(y + off, yv);
 #pragma unroll
@@ -767,7 +783,7 @@ extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
-    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
@@ -781,22 +797,24 @@ extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float*
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums, long long M,
-                                  int C, int relu, void* stream) {
+                                  int C, int relu, const float* gamma, const float* beta, void* stream) {
+    PDNN_REQUIRE(!(relu && y == nullptr) || (gamma != nullptr && beta != nullptr), "bn_bwd_reduce: y == NULL needs gamma and beta to rebuild the ReLU mask");
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
-    bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu);
+    bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,
                                  const float* sums, void* dx, void* dresidual, float* dgamma, float* dbeta, long long M, int C,
-                                 int relu, void* stream) {
+                                 int relu, const float* beta, void* stream) {
+    PDNN_REQUIRE(!(relu && y == nullptr) || beta != nullptr, "bn_bwd_apply: y == NULL needs beta to rebuild the ReLU mask");
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi_a; size_t smem_a;
     bn_reduce_cfg(C, &rpi_a, &smem_a);
     bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
-                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu);
+                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu, beta);
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream) {
@@ -976,7 +994,7 @@ extern "C" int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const floa
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
-    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     bn_fwd_apply_kernel<<<grid_for((M + rpi - 1) / rpi, 1, 148 * 8), 256, 0, ST(stream)>>>(

@@ -62,6 +62,10 @@ int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W
 int pdnn_conv_halo_supported(int batch, int H, int W, int C, int Kout, int R, int S, int pad);
 int pdnn_conv_halo_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
                               const pdnn_epilogue_t* epi, void* stream);
+/* Same conv fused with the statistics pass of the BatchNorm that follows: bn_stats [2][Kout] fp32 (zero on entry)
+ * receives sum and sum of squares of the stored bf16 output (then call pdnn_bn_fwd_apply directly). */
+int pdnn_conv_halo_fprop_stats_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
+                                    const pdnn_epilogue_t* epi, float* bn_stats, void* stream);
 
 /* Weight gradient of a 3x3 / stride 1 / pad 1 conv with halo reuse (csrc/conv_halo.cu): dw[Kout][3][3][C] fp32 +=
  * (red.add, caller zero-fills). C in {64, 128}, Kout % 64 == 0, see pdnn_conv_halo_wgrad_supported(). */
@@ -112,13 +116,15 @@ int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, con
 int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const float* beta, const void* residual, void* y,
                         float* mean_invstd, float* running_mean, float* running_var, long long M, int C,
                         float eps, float momentum, int relu, void* stream);
-/* sums: [2][C] fp32, zero on entry: sum(dz), sum(dz * xhat), dz = dy * (y > 0 if relu). */
+/* sums: [2][C] fp32, zero on entry: sum(dz), sum(dz * xhat), dz = dy * (y > 0 if relu).
+ * y may be NULL when the forward had no residual: the mask is then rebuilt from x (gamma*xhat + beta > 0), which
+ * saves reading y in both backward passes; gamma / beta are only read in that case. */
 int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums,
-                       long long M, int C, int relu, void* stream);
+                       long long M, int C, int relu, const float* gamma, const float* beta, void* stream);
 /* dx = gamma*invstd*(dz - sum_dz/M - xhat*sum_dzxhat/M); dresidual = dz (optional); dgamma/dbeta fp32. */
 int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd,
                       const float* gamma, const float* sums, void* dx, void* dresidual, float* dgamma,
-                      float* dbeta, long long M, int C, int relu, void* stream);
+                      float* dbeta, long long M, int C, int relu, const float* beta, void* stream);
 
 int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream);
 int pdnn_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream);

@@ -156,13 +156,22 @@ class Conv2d(Layer):
             self.w_pad[:, : self.kdim].copy_(self.weight.w.view(self.cout, self.kdim))
 
     # -- forward ---------------------------------------------------------------------------------
-    def forward(self, x):
+    def forward(self, x, bn=None):
+        """``bn``: the BatchNorm that consumes this conv's output; when the kernel can, it fills ``bn.stats`` from its
+        epilogue (``bn.stats_ready``) so that the BatchNorm skips its statistics pass."""
         self.x = x
         w = self.weight.w
         bias = self.bias.wf if self.bias is not None else None
+        if bn is not None:
+            bn.stats_ready = False
         if self.mode == "implicit":
             if self.halo_f:
-                F.conv_halo_fprop(x, w.view(self.cout, self.k, self.k, self.cin), out=self.y, bias=bias)
+                stats = None
+                if bn is not None and self.net.fuse_bn_stats:
+                    bn.stats.zero_()
+                    bn.stats_ready = True
+                    stats = bn.stats
+                F.conv_halo_fprop(x, w.view(self.cout, self.k, self.k, self.cin), out=self.y, bias=bias, bn_stats=stats)
             else:
                 F.conv_fprop(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, out=self.y, bias=bias)
         elif self.mode == "lowered":
@@ -269,15 +278,18 @@ class BatchNorm(Layer):
         self.dres = None
         self.x = None
         self.out_shape = in_shape
+        self.stats_ready = False
 
     def params(self):
         return [self.weight, self.bias]
 
     def forward(self, x, residual=None):
         self.x = x
+        self._had_residual = residual is not None
         F.bn_forward(x, self.weight.wf, self.bias.wf, relu=self.relu, residual=residual, eps=self.eps,
                      momentum=self.momentum, running_mean=self.running_mean, running_var=self.running_var,
-                     stats=self.stats, mean_invstd=self.mean_invstd, out=self.y)
+                     stats=self.stats, mean_invstd=self.mean_invstd, out=self.y, stats_ready=self.stats_ready)
+        self.stats_ready = False
         return self.y
 
     def backward(self, dy):
@@ -287,9 +299,11 @@ class BatchNorm(Layer):
         """Returns (dx, dresidual): dresidual is the gradient w.r.t. the tensor added before the ReLU."""
         if want_dresidual and self.dres is None:
             self.dres = torch.empty_like(self.dx)
-        F.bn_backward(self.x, self.y, dy, self.weight.wf, self.mean_invstd, relu=self.relu,
+        # without a residual the ReLU mask is rebuilt from x inside the kernels: y is not read again
+        y = self.y if (self._had_residual or not self.relu) else None
+        F.bn_backward(self.x, y, dy, self.weight.wf, self.mean_invstd, relu=self.relu,
                       want_dresidual=want_dresidual, sums=self.sums, dx=self.dx, dresidual=self.dres,
-                      dgamma=self.weight.g, dbeta=self.bias.g)
+                      dgamma=self.weight.g, dbeta=self.bias.g, beta=self.bias.wf)
         self.net.grad_ready(self.bias)
         self.net.grad_ready(self.weight)
         return self.dx, (self.dres if want_dresidual else None)
@@ -464,9 +478,9 @@ class BasicBlock(Layer):
         return max(l.scratch_elems() for l in self.sublayers() if isinstance(l, Conv2d))
 
     def forward(self, x):
-        a1 = self.bn1.forward(self.conv1.forward(x))
-        o2 = self.conv2.forward(a1)
-        s = self.sc_bn.forward(self.sc_conv.forward(x)) if self.has_sc else x
+        a1 = self.bn1.forward(self.conv1.forward(x, bn=self.bn1))
+        o2 = self.conv2.forward(a1, bn=self.bn2)
+        s = self.sc_bn.forward(self.sc_conv.forward(x, bn=self.sc_bn)) if self.has_sc else x
         return self.bn2.forward(o2, residual=s)
 
     def backward(self, dy):
@@ -519,10 +533,10 @@ class Bottleneck(Layer):
         return max(l.scratch_elems() for l in self.sublayers() if isinstance(l, Conv2d))
 
     def forward(self, x):
-        a1 = self.bn1.forward(self.conv1.forward(x))
-        a2 = self.bn2.forward(self.conv2.forward(a1))
-        o3 = self.conv3.forward(a2)
-        s = self.sc_bn.forward(self.sc_conv.forward(x)) if self.has_sc else x
+        a1 = self.bn1.forward(self.conv1.forward(x, bn=self.bn1))
+        a2 = self.bn2.forward(self.conv2.forward(a1, bn=self.bn2))
+        o3 = self.conv3.forward(a2, bn=self.bn3)
+        s = self.sc_bn.forward(self.sc_conv.forward(x, bn=self.sc_bn)) if self.has_sc else x
         return self.bn3.forward(o3, residual=s)
 
     def backward(self, dy):

@@ -55,6 +55,7 @@ class Network:
         self.dlogits = None
         self.x_in = None
         self.keep_col = True   # keep im2col matrices of lowered convs for backward (memory for time)
+        self.fuse_bn_stats = os.environ.get("PDNN_NO_BN_FUSE") != "1"   # conv epilogue produces the following BN's statistics
         self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
 
     # ---- construction ---------------------------------------------------------------------------
@@ -242,8 +243,12 @@ class Network:
 
     def forward(self, x_nchw_f32):
         x = self.stage_input(x_nchw_f32)
-        for layer in self.layers:
-            x = layer.forward(x)
+        layers = self.layers
+        for i, layer in enumerate(layers):
+            if isinstance(layer, L.Conv2d) and i + 1 < len(layers) and isinstance(layers[i + 1], L.BatchNorm):
+                x = layer.forward(x, bn=layers[i + 1])     # the conv epilogue may produce that BatchNorm's statistics
+            else:
+                x = layer.forward(x)
         self.logits = x
         return x
 

@@ -70,6 +70,7 @@ _SIGS = {
     "pdnn_conv_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_supported": [_I] * 8,
     "pdnn_conv_halo_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
+    "pdnn_conv_halo_fprop_stats_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P, _P],
     "pdnn_conv_halo_wgrad_supported": [_I] * 8,
     "pdnn_conv_halo_wgrad_bf16": [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P],
     "pdnn_conv_wgrad_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
@@ -85,8 +86,8 @@ _SIGS = {
     "pdnn_col2im_f32": [_P, _P] + [_I] * 11 + [_P],
     "pdnn_bn_fwd_stats": [_P, _P, _L, _I, _P],
     "pdnn_bn_fwd_apply": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _F, _F, _I, _P],
-    "pdnn_bn_bwd_reduce": [_P, _P, _P, _P, _P, _L, _I, _I, _P],
-    "pdnn_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _I, _P],
+    "pdnn_bn_bwd_reduce": [_P, _P, _P, _P, _P, _L, _I, _I, _P, _P, _P],
+    "pdnn_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _I, _P, _P],
     "pdnn_relu_fwd": [_P, _P, _L, _P],
     "pdnn_relu_bwd": [_P, _P, _P, _L, _P],
     "pdnn_relu_fwd_f32": [_P, _P, _L, _P],

@@ -85,14 +85,19 @@ def conv_halo_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
     return bool(_lib.lib().pdnn_conv_halo_supported(n, h, w, c, kout, R, S, pad))
 
 
-def conv_halo_fprop(x, w, *, out=None, bias=None, relu=False, residual=None):
-    """3x3/s1/p1 conv through the halo-reuse kernel (C in {64,128}): x [N,H,W,C] bf16, w [Kout,3,3,C] bf16."""
+def conv_halo_fprop(x, w, *, out=None, bias=None, relu=False, residual=None, bn_stats=None):
+    """3x3/s1/p1 conv through the halo-reuse kernel (C in {64,128}): x [N,H,W,C] bf16, w [Kout,3,3,C] bf16.
+    ``bn_stats`` ([2, Kout] fp32, zeroed by the caller) additionally receives the per-channel sum / sum of squares of
+    the output, i.e. the statistics pass of the BatchNorm that follows."""
     n, h, wd, c = x.shape
     kout = w.shape[0]
     if out is None:
         out = torch.empty(n, h, wd, kout, device=x.device, dtype=BF16)
     e = _epi(out, kout, 0, relu, 1.0, bias, residual)
-    call("pdnn_conv_halo_fprop_bf16", x, w, n, h, wd, c, kout, C.byref(e), stream_ptr())
+    if bn_stats is None:
+        call("pdnn_conv_halo_fprop_bf16", x, w, n, h, wd, c, kout, C.byref(e), stream_ptr())
+    else:
+        call("pdnn_conv_halo_fprop_stats_bf16", x, w, n, h, wd, c, kout, C.byref(e), bn_stats, stream_ptr())
     return out
 
 
@@ -196,27 +201,30 @@ def col2im(dcol, x_shape, R, S, stride, pad, out=None):
 
 
 def bn_forward(x, gamma, beta, *, relu=False, residual=None, eps=1e-5, momentum=0.1, running_mean=None,
-               running_var=None, stats=None, mean_invstd=None, out=None):
-    """Training-mode BatchNorm over all but the last dim of NHWC bf16 x. Returns (y, mean_invstd)."""
+               running_var=None, stats=None, mean_invstd=None, out=None, stats_ready=False):
+    """Training-mode BatchNorm over all but the last dim of NHWC bf16 x. Returns (y, mean_invstd).
+    ``stats_ready``: ``stats`` already holds sum / sum of squares (produced by the conv epilogue): skip that pass."""
     c = x.shape[-1]
     m = x.numel() // c
     if stats is None:
         stats = torch.zeros(2, c, device=x.device, dtype=F32)
-    else:
+    elif not stats_ready:
         stats.zero_()
     if mean_invstd is None:
         mean_invstd = torch.empty(2, c, device=x.device, dtype=F32)
     if out is None:
         out = torch.empty_like(x)
     st = stream_ptr()
-    call("pdnn_bn_fwd_stats", x, stats, m, c, st)
+    if not stats_ready:
+        call("pdnn_bn_fwd_stats", x, stats, m, c, st)
     call("pdnn_bn_fwd_apply", x, stats, gamma, beta, residual, out, mean_invstd, running_mean, running_var, m, c,
          eps, momentum, int(relu), st)
     return out, mean_invstd
 
 
 def bn_backward(x, y, dy, gamma, mean_invstd, *, relu=False, want_dresidual=False, sums=None, dx=None,
-                dresidual=None, dgamma=None, dbeta=None):
+                dresidual=None, dgamma=None, dbeta=None, beta=None):
+    """``y=None`` (allowed when the forward had no residual and ``beta`` is given) rebuilds the ReLU mask from x."""
     c = x.shape[-1]
     m = x.numel() // c
     if sums is None:
@@ -232,9 +240,9 @@ def bn_backward(x, y, dy, gamma, mean_invstd, *, relu=False, want_dresidual=Fals
     if dbeta is None:
         dbeta = torch.empty(c, device=x.device, dtype=F32)
     st = stream_ptr()
-    call("pdnn_bn_bwd_reduce", x, y, dy, mean_invstd, sums, m, c, int(relu), st)
+    call("pdnn_bn_bwd_reduce", x, y, dy, mean_invstd, sums, m, c, int(relu), gamma, beta, st)
     call("pdnn_bn_bwd_apply", x, y, dy, mean_invstd, gamma, sums, dx, dresidual if want_dresidual else None,
-         dgamma, dbeta, m, c, int(relu), st)
+         dgamma, dbeta, m, c, int(relu), beta, st)
     return dx, dresidual, dgamma, dbeta
 
 
