@@ -242,7 +242,7 @@ __global__ void col2im_kernel(const T* __restrict__ dcol, T* __restrict__ dx, in
 // ------------------------------------------------------------------------------------------------
 // Pass 1: per-channel sum and sum of squares. Each thread owns 8 channels of a strided set of rows,
 // the block folds its row groups through shared memory, one atomicAdd per channel per block.
-template <int MODE>   // 0: stats of x ; 1: backward sums (dz, dz*xhat)
+template <int MODE>   // 0: stats of x ; 1: backward sums (dz, dz*xhat), ReLU mask from y ; 2: same, mask rebuilt from x
 __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
                                                         const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
                                                         float* __restrict__ out, long long M, int C, int relu,
@@ -259,13 +259,14 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
         for (int j = 0; j < 8; ++j) { a0[j] = 0.f; a1[j] = 0.f; }
         float mean[8], inv[8], sc[8], sf[8];
         // without a residual the ReLU mask is a function of x alone (y > 0 <=> gamma*xhat + beta > 0): y is not read
-        const bool mask_from_x = (MODE == 1) && relu && (y == nullptr);
-        if (MODE == 1) {
+        constexpr bool mask_from_x = (MODE == 2);
+        if (MODE >= 1) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 mean[j] = mean_invstd[ct * 8 + j]; inv[j] = mean_invstd[C + ct * 8 + j];
                 sc[j] = 0.f; sf[j] = 0.f;
                 if (mask_from_x) { sc[j] = gamma[ct * 8 + j] * inv[j]; sf[j] = beta[ct * 8 + j] - mean[j] * sc[j]; }
+                (void)sc[j]; (void)sf[j];
             }
         }
         for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += (long long)gridDim.x * rpi) {
@@ -803,7 +804,10 @@ extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, 
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
-    bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
+    if (relu && y == nullptr)
+        bn_reduce_kernel<2><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
+    else
+        bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,

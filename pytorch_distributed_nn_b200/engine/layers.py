@@ -300,7 +300,7 @@ class BatchNorm(Layer):
         if want_dresidual and self.dres is None:
             self.dres = torch.empty_like(self.dx)
         # without a residual the ReLU mask is rebuilt from x inside the kernels: y is not read again
-        y = self.y if (self._had_residual or not self.relu) else None
+        y = self.y if (self._had_residual or not self.relu or not self.net.bn_mask_from_x) else None
         F.bn_backward(self.x, y, dy, self.weight.wf, self.mean_invstd, relu=self.relu,
                       want_dresidual=want_dresidual, sums=self.sums, dx=self.dx, dresidual=self.dres,
                       dgamma=self.weight.g, dbeta=self.bias.g, beta=self.bias.wf)

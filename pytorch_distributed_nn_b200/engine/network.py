@@ -55,7 +55,10 @@ class Network:
         self.dlogits = None
         self.x_in = None
         self.keep_col = True   # keep im2col matrices of lowered convs for backward (memory for time)
-        self.fuse_bn_stats = os.environ.get("PDNN_NO_BN_FUSE") != "1"   # conv epilogue produces the following BN's statistics
+        # conv epilogue produces the following BN's statistics: measured SLOWER on B200 (the warp-shuffle column sums make
+        # the epilogue warps the bottleneck: 168 us vs 81 us + 19 us for the separate pass), so it is opt-in
+        self.fuse_bn_stats = os.environ.get("PDNN_BN_FUSE") == "1"
+        self.bn_mask_from_x = os.environ.get("PDNN_BN_MASK_FROM_X", "1") == "1"   # BN backward without re-reading y (no residual)
         self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
 
     # ---- construction ---------------------------------------------------------------------------
