@@ -258,7 +258,8 @@ def main():
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "final_loss": losses[-1]},
             "gpu_launches": int(launches),
             "gpu_launches_per_step": round(launches / args.steps, 1),
-            "last_master_result": {"selected_mask": res[0], "kill_mask": res[1], "n_received": res[2], "step": res[3]},
+            "last_master_result": {"selected_mask": res[0], "kill_mask": res[1], "n_received": res[2], "step": res[3],
+                                   "device_timeline_us": ps.last_timing_us},
             "clocks": clocks,
         }
         if cdf is not None:

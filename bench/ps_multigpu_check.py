@@ -92,7 +92,7 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
         if st != s:
             ok = False
             log.append(f"step {s}: master reported step {st}")
-        if delay_spec:
+        if delay_spec and delay_spec.startswith("const"):
             late = n_workers - 1
             if not (kill >> late & 1) or (sel >> late & 1) or nrecv != k:
                 ok = False
@@ -100,6 +100,12 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
             if ps.is_worker and ps.worker_id == late and int(ps.flags[W_CLOSED]) != s:
                 ok = False
                 log.append(f"rank {rank} step {s}: closed word = {int(ps.flags[W_CLOSED])}")
+        elif delay_spec:
+            # randomised delays: whoever is selected, exactly k sets count, the rest are named in the kill mask, and the
+            # update above already matched the oracle for that selection
+            if nrecv != k or bin(sel).count("1") != k or (sel | kill) != (1 << n_workers) - 1 or (sel & kill):
+                ok = False
+                log.append(f"step {s}: inconsistent masks sel={sel:b} kill={kill:b} nrecv={nrecv}")
         else:
             if sel != (1 << n_workers) - 1 or kill != 0:
                 ok = False
@@ -133,6 +139,9 @@ def main():
         # the last worker is delayed by 30 ms on the device; k = n-1
         results["k_of_n_kill_colocated"] = run_case(args.network, args.batch, rank, world, args.steps, n_workers - 1,
                                                     f"const:ranks={n_workers}:ms=30", "fp32", True)
+        # stress: random per-(worker, step) delays, k = n-1: the selection changes from step to step
+        results["k_of_n_random_delays"] = run_case(args.network, args.batch, rank, world, 8, n_workers - 1,
+                                                   "uniform:lo=0:hi=20:p=0.7:seed=5", "fp32", True)
     if world >= 3:
         results["all_n_master_only_rank0"] = run_case(args.network, args.batch, rank, world, args.steps, None, "", "fp32", False)
     if rank == 0:

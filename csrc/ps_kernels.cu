@@ -122,6 +122,10 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
             margs.result[1] = kill;
             margs.result[2] = count;
             margs.result[3] = err ? 0xDEADu : cur_step;
+            // device-side timeline (globaltimer, microseconds): how long the master waited for the k-th arrival
+            const uint64_t t1 = globaltimer_ns();
+            margs.result[4] = (uint32_t)((t1 - t0) / 1000ull);
+            ctl[5] = (uint32_t)(t1 / 1000ull);
             ctl[CTL_MASK] = mask;
             __threadfence();
             asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ctl + CTL_MASK_STEP), "r"(cur_step) : "memory");
@@ -231,6 +235,7 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
         const uint32_t done = atom_add_acqrel_gpu(ctl + CTL_DONE, 1u) + 1u;
         if (done == gridDim.x) {
             ctl[CTL_DONE] = 0;
+            margs.result[5] = (uint32_t)(globaltimer_ns() / 1000ull) - ctl[5];   // reduce + update + broadcast, microseconds
             if (a.step_ptr != nullptr) st_relaxed_sys(a.step_ptr, cur_step + 1u);
             __threadfence_system();
             for (int w = 0; w < a.n_workers; ++w)

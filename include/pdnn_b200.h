@@ -210,7 +210,9 @@ typedef struct pdnn_ps_master {
  * stores or one multimem store), then release the workers (weights_ready = step+1).
  * ref: SyncReplicasMaster_NN.train hot loop, pytorch_code/sync_replicas_master_nn.py:117-228
  * (Waitany/aggregate/kill/update/Bcast) and MPI_code/src/distributed/sync_replicas_master_nn.h:46-137.
- * result_host_or_dev (device, 4 words): [0]=selected mask, [1]=kill mask, [2]=#received, [3]=step. */
+ * result (device, 8 words): [0]=selected mask, [1]=kill mask, [2]=#received, [3]=step (0xDEAD: the hard timeout
+ * expired before k gradient sets arrived), [4]=microseconds waited for the k-th arrival, [5]=microseconds of
+ * reduce + update + broadcast (device %globaltimer). */
 int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* stream);
 
 /* Worker: block the stream until *ready_flag >= step (ref: distributed_worker.py:202-208 irecv tag 10). */

@@ -163,7 +163,7 @@ class B200ParameterServer:
             m.deadline_ns = self.deadline_ns
             m.max_ctas = 0
             self._margs = m
-            self.result = self.flags[M_RESULT: M_RESULT + 4]
+            self.result = self.flags[M_RESULT: M_RESULT + 8]
             self.history = []
 
     def _initial_broadcast(self, group):
@@ -275,8 +275,12 @@ class B200ParameterServer:
 
     def last_result(self):
         """(selected_mask, kill_mask, n_received, step) of the most recent master step (synchronises)."""
-        r = self.result.cpu().tolist()
-        return tuple(int(v) & 0xFFFFFFFF for v in r)
+        r = [int(v) & 0xFFFFFFFF for v in self.result.cpu().tolist()]
+        if r[3] == 0xDEAD:
+            raise RuntimeError("parameter-server master timed out: fewer than k gradient sets arrived (a worker died or hung); "
+                               f"arrived mask={r[0]:b}")
+        self.last_timing_us = {"wait_for_kth_arrival": r[4], "reduce_update_broadcast": r[5]}
+        return tuple(r[:4])
 
     def master_state_dict(self):
         return self.net.state_dict()

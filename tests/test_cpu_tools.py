@@ -1,0 +1,50 @@
+"""CPU: tooling -- cluster config / host files, experiment configs, straggler-study driver (dry run), plot scripts."""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cluster_cfg_interpolation_and_host_files(tmp_path):
+    sys.path.insert(0, ROOT)
+    from tools.cluster import get_hosts, load_cfg
+    cfg_path = tmp_path / "c.cfg"
+    cfg_path.write_text('{"name": "t", "hosts": ["10.0.0.1", "10.0.0.2"], "gpus_per_host": 8, "train_dir": "/tmp/%(name)s_x"}')
+    cfg = load_cfg(str(cfg_path))
+    assert cfg["train_dir"] == "/tmp/t_x"
+    cwd = os.getcwd()
+    os.chdir(tmp_path)
+    try:
+        get_hosts(cfg)
+        assert open("hosts_address").read().splitlines() == ["10.0.0.1 slots=8", "10.0.0.2 slots=8"]
+        assert open("hosts_alias").read().split() == ["deeplearning-worker0", "deeplearning-worker1"]
+    finally:
+        os.chdir(cwd)
+
+
+def test_experiment_configs_load_and_map_to_commands():
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench", "straggler_study.py"), "--dry-run"] +
+                       [os.path.join(ROOT, "configs", d, f) for d in ("k_sweep", "interval_sweep", "time_cdf")
+                        for f in sorted(os.listdir(os.path.join(ROOT, "configs", d)))],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    lines = [l for l in r.stdout.splitlines() if l.startswith("#")]
+    assert len(lines) == 18
+    assert any("--num-aggregate 6" in l for l in lines) and any("--interval-ms 5" in l for l in lines)
+    assert any("--worker-times-cdf" in l and "pareto" in l for l in lines)
+
+
+def test_plot_scripts_summarise_reference_file_formats(tmp_path):
+    sys.path.insert(0, ROOT)
+    from tools.plot_time_loss import main as plot_main
+    from tools.visualize_timeline import summarize
+    out = tmp_path / "outfiles"
+    out.mkdir()
+    (out / "time_loss_out_SyncReplicasWithBackup2_6").write_text("1 10.0 2.30 0.90\n2 20.0 2.10 0.80\n")
+    series = plot_main(str(out), str(tmp_path / "p.png"))
+    assert series["SyncReplicasWithBackup2_6"][-1][2] == 2.10
+    tl = tmp_path / "timeline"
+    tl.write_text("0.0 1 1\n1.0 1 0\n2.0 1 0\n5.0 2 1\n6.0 2 0\n")
+    steps, avg = summarize(str(tl))
+    assert abs(avg - 1.5) < 1e-9 and len(steps[1]["arrivals"]) == 2

@@ -137,11 +137,11 @@ def test_master_kernel_k_of_n_matches_oracle(avg_mode):
     m0 = torch.randn(n, device=dev) * 0.1
     master_w, mom = w0.clone(), m0.clone()
     ctl = torch.zeros(64, device=dev, dtype=torch.int32)
-    result = torch.zeros(4, device=dev, dtype=torch.int32)
+    result = torch.zeros(8, device=dev, dtype=torch.int32)
     args = _master_args(nw, n, k, grads, flags, weights, ready, closed, master_w, mom, ctl, step, AVG_MODES[avg_mode])
     _lib.call("pdnn_ps_master_step", C.byref(args), result.data_ptr(), _lib.stream_ptr())
     torch.cuda.synchronize()
-    sel, kill, nrecv, st = [int(v) for v in result.tolist()]
+    sel, kill, nrecv, st = [int(v) for v in result.tolist()[:4]]
     assert (sel, kill, nrecv, st) == (0b1101, 0b0010, 3, 7)
     assert closed.tolist() == [0, 7, 0, 0]                 # only the straggler is told to abandon step 7
     assert ready.tolist() == [8, 8, 8, 8]                  # everybody is released into step 8
