@@ -36,23 +36,8 @@ struct HaloParams {
     const __nv_bfloat16* residual;
     const uint32_t* guard_closed;
     const uint32_t* guard_step;
-    int use_base_offset;
     float* bn_stats;     // optional [2][Kout]: per-channel sum and sum of squares of the (bf16-rounded) output
 };
-
-__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr, int use_base_offset) {
-    // K-major, 128B swizzle, SBO = 1024 (8 rows of 128 B); the start address may sit on any 128-byte row boundary
-    // (+ the 32-byte K step inside the row). base_offset stays 0 (see the file header); the switch exists for the
-    // diagnostic only.
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)1 << 16;                          // LBO (unused for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;                // SBO
-    d |= (uint64_t)1 << 46;                          // descriptor version
-    if (use_base_offset) d |= (uint64_t)((saddr >> 7) & 7) << 49;         // base offset
-    d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
-    return d;
-}
 
 constexpr int HALO_THREADS = 256;
 constexpr int HALO_BN = 64;
@@ -331,10 +316,6 @@ static int conv_halo_fprop_impl(const void* x, const void* wgt, int batch, int H
     p.residual = reinterpret_cast<const __nv_bfloat16*>(epi->residual);
     p.guard_closed = epi->guard_closed; p.guard_step = epi->guard_step;
     p.bn_stats = bn_stats;
-    {
-        const char* e = getenv("PDNN_HALO_BASE_OFFSET");
-        p.use_base_offset = e != nullptr ? atoi(e) : 0;
-    }
     CUtensorMap tmX, tmW;
     {
         long long dims[4] = {C, W, H, batch};

@@ -22,7 +22,6 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-import time
 from typing import Callable, Optional
 
 import torch
