@@ -235,6 +235,27 @@ def conv_halo_wgrad():
 
 
 @case
+def conv_strided():
+    """Stride-2 convs as implicit GEMM: TMA element strides instead of an im2col buffer."""
+    F = _F()
+    ok = True
+    for (n, h, c, k, r, pad) in [(8, 32, 64, 128, 3, 1), (8, 16, 128, 256, 3, 1), (16, 8, 256, 512, 3, 1), (8, 32, 64, 128, 1, 0),
+                                 (16, 8, 256, 512, 1, 0)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        w = (torch.randn(k, r, r, c, device="cuda") / (r * c ** 0.5)).bfloat16()
+        xr = x.float().permute(0, 3, 1, 2)
+        wr = w.float().permute(0, 3, 1, 2).requires_grad_(True)
+        yr = torch.nn.functional.conv2d(xr, wr, stride=2, padding=pad)
+        y = F.conv_fprop_strided(x, w, pad=pad, stride=2)
+        ok &= report(f"conv_s2_fprop[n{n} {h}x{h} c{c} k{k} r{r}]", rel_err(y, yr.permute(0, 2, 3, 1)), 1.5e-2)
+        dy = torch.randn(y.shape, device="cuda").bfloat16()
+        yr.backward(dy.float().permute(0, 3, 1, 2))
+        dw = F.conv_wgrad_strided(x, dy, R=r, S=r, pad=pad, stride=2)
+        ok &= report(f"conv_s2_wgrad[n{n} {h}x{h} c{c} k{k} r{r}]", rel_err(dw, wr.grad.permute(0, 2, 3, 1)), 5e-3)
+    return ok
+
+
+@case
 def conv_dgrad():
     F = _F()
     ok = True

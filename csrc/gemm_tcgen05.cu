@@ -36,7 +36,8 @@ struct GemmParams {
     int m_tiles, n_tiles, k_splits;
     int k_iters_total, k_iters_per_split;
     // geometry of the activation operand in the conv modes
-    int H, W, C, R, S, pad;
+    int H, W, C, R, S, pad;   // H, W: OUTPUT map (tile decode); the activation tensor map carries the input geometry
+    int stride;               // conv stride (1 or 2): the TMA box walks the input with this element stride
     int box_h, box_n;        // pixel box (box_w == W)
     int cblks;               // C / 64 (OP_CONVK) or C / BN (OP_CONVMN)
     // epilogue
@@ -162,7 +163,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         const int cb = kit - rs * p.cblks;
                         const int r = rs / p.S;
                         const int s = rs - r * p.S;
-                        tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 + r - p.pad, a_n0);
+                        tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
                     }
                     // ---- B ----
                     if (BMODE == OP_K2D) {
@@ -178,7 +179,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
                             tma_load_4d(sb + j * 8192, &tmB, fb, b_c0 + j * 64, b_s - p.pad,
-                                        h0 + b_r - p.pad, n0);
+                                        h0 * p.stride + b_r - p.pad, n0);
                     } else if (BMODE == OP_CONVMN_G3) {
                         const int p0 = kit * BLOCK_K;
                         const int n0 = p0 / hw;
@@ -187,7 +188,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         const int cb = nt - r * p.cblks;
 #pragma unroll
                         for (int j = 0; j < 3; ++j)
-                            tma_load_4d(sb + j * 8192, &tmB, fb, cb * 64, j - p.pad, h0 + r - p.pad, n0);
+                            tma_load_4d(sb + j * 8192, &tmB, fb, cb * 64, j - p.pad, h0 * p.stride + r - p.pad, n0);
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -371,7 +372,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // bf16 tensor map, up to 4 dims, dims[0] innermost (contiguous). strides in elements for dims 1..rank-1.
 static int make_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const long long* dims,
-                          const long long* strides_elems, const int* box) {
+                          const long long* strides_elems, const int* box, const int* elem_strides = nullptr) {
     EncodeTiledFn enc = get_encode_fn();
     PDNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
     cuuint64_t gdim[5];
@@ -381,7 +382,7 @@ static int make_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const lon
     for (int i = 0; i < rank; ++i) {
         gdim[i] = (cuuint64_t)dims[i];
         bdim[i] = (cuuint32_t)box[i];
-        estr[i] = 1;
+        estr[i] = elem_strides != nullptr ? (cuuint32_t)elem_strides[i] : 1;
         if (i > 0) gstr[i - 1] = (cuuint64_t)strides_elems[i] * 2ull;
     }
     PDNN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base pointer must be 16-byte aligned");
@@ -503,6 +504,7 @@ extern "C" int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, cons
         if (int rc = make_tmap_bf16(&tmB, B, 2, dims, str, box)) return rc;
     }
     GemmParams p{};
+    p.stride = 1;
     p.M = M; p.N = N; p.K = K;
     p.m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
     p.n_tiles = (N + bn - 1) / bn;
@@ -542,6 +544,7 @@ extern "C" int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, i
     PDNN_REQUIRE(C % 64 == 0, "conv_fprop: C=%d must be a multiple of 64 (use the im2col path)", C);
     PDNN_REQUIRE(2 * pad == R - 1 && 2 * pad == S - 1, "conv_fprop: only 'same' stride-1 geometry (R=%d S=%d pad=%d)", R, S, pad);
     GemmParams p{};
+    p.stride = 1;
     PDNN_REQUIRE(pixel_box(H, W, batch, BLOCK_M, &p.box_h, &p.box_n) == 0,
                  "conv_fprop: %dx%d images (batch %d) do not tile into 128-pixel boxes", H, W, batch);
     const long long Mll = (long long)batch * H * W;
@@ -580,6 +583,7 @@ extern "C" int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, in
     PDNN_REQUIRE(Kout % 8 == 0, "conv_wgrad: Kout=%d must be a multiple of 8", Kout);
     PDNN_REQUIRE(epi->out_mode == 2, "conv_wgrad accumulates with fp32 red.add (out_mode must be 2)");
     GemmParams p{};
+    p.stride = 1;
     PDNN_REQUIRE(pixel_box(H, W, batch, BLOCK_K, &p.box_h, &p.box_n) == 0,
                  "conv_wgrad: %dx%d images (batch %d) do not tile into 64-pixel boxes", H, W, batch);
     const long long pix = (long long)batch * H * W;
@@ -608,6 +612,91 @@ extern "C" int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, in
     }
     p.k_iters_total = (int)(pix / BLOCK_K);
     p.H = H; p.W = W; p.C = C; p.R = R; p.S = S; p.pad = pad;
+    fill_epilogue(p, epi);
+    p.k_splits = choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits);
+    finish_splits(p);
+    if (g3) return launch_gemm<OP_MN2D, OP_CONVMN_G3, 192>(tmA, tmB, p, epi->max_ctas, stream);
+    return dispatch_bn<OP_MN2D, OP_CONVMN>(bn, tmA, tmB, p, epi->max_ctas, stream);
+}
+
+
+// Output-geometry helper of the strided forms: the TMA box spans `stride * count` input elements along W / H and
+// picks every stride-th one (elementStrides), so shared memory receives exactly the `count` pixels an output tile needs.
+static int strided_box(int count, int stride) { return stride == 1 ? count : stride * count; }
+
+// Strided convolution forward as implicit GEMM (no im2col): y[n,oh,ow,:] = sum x[n, oh*stride+r-pad, ow*stride+s-pad, :] w[k,r,s,:]
+extern "C" int pdnn_conv_fprop_strided_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout, int R, int S,
+                                            int pad, int stride, const pdnn_epilogue_t* epi, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(C % 64 == 0, "conv_fprop_strided: C=%d must be a multiple of 64", C);
+    PDNN_REQUIRE(stride >= 1 && stride <= 2, "conv_fprop_strided: stride %d not supported", stride);
+    const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+    GemmParams p{};
+    p.stride = stride;
+    PDNN_REQUIRE(pixel_box(OH, OW, batch, BLOCK_M, &p.box_h, &p.box_n) == 0,
+                 "conv_fprop_strided: %dx%d outputs (batch %d) do not tile into 128-pixel boxes", OH, OW, batch);
+    const long long Mll = (long long)batch * OH * OW;
+    PDNN_REQUIRE(Mll % BLOCK_M == 0 && Mll < (1ll << 31), "conv_fprop_strided: pixel count must be a multiple of 128");
+    PDNN_REQUIRE(strided_box(OW, stride) <= 256 && strided_box(p.box_h, stride) <= 256, "conv_fprop_strided: box too large");
+    const int bn = pick_bn(Kout);
+    CUtensorMap tmA, tmB;
+    {
+        long long dims[4] = {C, W, H, batch};
+        long long str[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int box[4] = {64, strided_box(OW, stride), strided_box(p.box_h, stride), p.box_n};
+        int es[4] = {1, stride, stride, 1};
+        if (int rc = make_tmap_bf16(&tmA, x, 4, dims, str, box, es)) return rc;
+        long long wd[2] = {(long long)R * S * C, Kout};
+        long long ws[2] = {1, (long long)R * S * C};
+        int wb[2] = {64, bn};
+        if (int rc = make_tmap_bf16(&tmB, wgt, 2, wd, ws, wb)) return rc;
+    }
+    p.M = (int)Mll; p.N = Kout; p.K = R * S * C;
+    p.m_tiles = p.M / BLOCK_M;
+    p.n_tiles = (Kout + bn - 1) / bn;
+    p.k_iters_total = R * S * (C / 64);
+    p.k_splits = 1;
+    finish_splits(p);
+    p.H = OH; p.W = OW; p.C = C; p.R = R; p.S = S; p.pad = pad;
+    p.cblks = C / 64;
+    fill_epilogue(p, epi);
+    return dispatch_bn<OP_CONVK, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
+}
+
+// Weight gradient of the strided conv: dw[k,r,s,c] += sum dy[n,oh,ow,k] x[n, oh*stride+r-pad, ow*stride+s-pad, c]
+extern "C" int pdnn_conv_wgrad_strided_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout, int R, int S,
+                                            int pad, int stride, const pdnn_epilogue_t* epi, int k_splits, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(C % 64 == 0 && Kout % 8 == 0, "conv_wgrad_strided: C=%d / Kout=%d not supported", C, Kout);
+    PDNN_REQUIRE(epi->out_mode == 2, "conv_wgrad_strided accumulates with fp32 red.add (out_mode must be 2)");
+    PDNN_REQUIRE(stride >= 1 && stride <= 2, "conv_wgrad_strided: stride %d not supported", stride);
+    const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+    GemmParams p{};
+    p.stride = stride;
+    PDNN_REQUIRE(pixel_box(OH, OW, batch, BLOCK_K, &p.box_h, &p.box_n) == 0,
+                 "conv_wgrad_strided: %dx%d outputs (batch %d) do not tile into 64-pixel boxes", OH, OW, batch);
+    const long long pix = (long long)batch * OH * OW;
+    PDNN_REQUIRE(pix % BLOCK_K == 0 && pix < (1ll << 31), "conv_wgrad_strided: pixel count must be a multiple of 64");
+    const bool g3 = (S == 3 && C <= 128);
+    const int bn = g3 ? 192 : ((C % 256 == 0) ? 256 : (C % 128 == 0 ? 128 : 64));
+    CUtensorMap tmA, tmB;
+    {
+        long long ad[2] = {Kout, pix};
+        long long as[2] = {1, Kout};
+        int ab[2] = {64, 64};
+        if (int rc = make_tmap_bf16(&tmA, dy, 2, ad, as, ab)) return rc;
+        long long dims[4] = {C, W, H, batch};
+        long long str[4] = {1, C, (long long)W * C, (long long)H * W * C};
+        int box[4] = {64, strided_box(OW, stride), strided_box(p.box_h, stride), p.box_n};
+        int es[4] = {1, stride, stride, 1};
+        if (int rc = make_tmap_bf16(&tmB, x, 4, dims, str, box, es)) return rc;
+    }
+    p.M = Kout; p.N = R * S * C; p.K = (int)pix;
+    p.m_tiles = (Kout + BLOCK_M - 1) / BLOCK_M;
+    if (g3) { p.cblks = C / 64; p.n_tiles = R * p.cblks; }
+    else { p.cblks = C / bn; p.n_tiles = R * S * p.cblks; }
+    p.k_iters_total = (int)(pix / BLOCK_K);
+    p.H = OH; p.W = OW; p.C = C; p.R = R; p.S = S; p.pad = pad;
     fill_epilogue(p, epi);
     p.k_splits = choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits);
     finish_splits(p);

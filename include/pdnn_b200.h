@@ -78,6 +78,14 @@ int pdnn_conv_halo_wgrad_bf16(const void* x, const void* dy, int batch, int H, i
 int pdnn_conv_wgrad_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout,
                          int R, int S, int pad, const pdnn_epilogue_t* epi, int k_splits, void* stream);
 
+/* Strided (stride 1 or 2) convolution forward / weight gradient as implicit GEMM without an im2col buffer: the
+ * activation tensor map walks the input with TMA element strides. H, W are the INPUT map; outputs have
+ * OH = (H + 2 pad - R) / stride + 1 rows. ref: the stride-2 3x3 convs and 1x1 shortcuts of resnet.py:19,27. */
+int pdnn_conv_fprop_strided_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout, int R, int S,
+                                 int pad, int stride, const pdnn_epilogue_t* epi, void* stream);
+int pdnn_conv_wgrad_strided_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout, int R, int S,
+                                 int pad, int stride, const pdnn_epilogue_t* epi, int k_splits, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Layer kernels (csrc/nn_kernels.cu)
  * ------------------------------------------------------------------------------------------- */

@@ -108,10 +108,16 @@ class Conv2d(Layer):
                 F.conv_halo_supported((n, h, w, cout), cin, k, k, pad)
             self.halo_w = net.use_halo and net.device.type == "cuda" and os.environ.get("PDNN_NO_HALO_WGRAD") != "1" and \
                 F.conv_halo_wgrad_supported(in_shape, cout, k, k, pad)
+        elif stride == 2 and cin % 64 == 0 and net.use_strided and self._tileable(n, self.oh, self.ow):
+            # implicit GEMM with TMA element strides (fprop, wgrad): no im2col matrix; dgrad stays GEMM + col2im
+            self.mode = "strided"
         else:
             self.mode = "lowered"
         self.y = torch.empty(self.out_shape, device=dev, dtype=dt)
         self.dx = None if first else torch.empty(in_shape, device=dev, dtype=dt)
+        if self.mode == "strided":
+            self.kpad = self.kdim
+            self.lowered_copy = True      # the dgrad GEMM output (dcol) lives in the shared scratch
         if self.mode == "lowered":
             self.kpad = _round_up(self.kdim, 8)
             self.lowered_copy = not (k == 1 and stride == 1)   # 1x1/s1 reads x in place
@@ -144,7 +150,7 @@ class Conv2d(Layer):
         return [self.weight] + ([self.bias] if self.bias is not None else [])
 
     def scratch_elems(self):
-        if self.mode == "implicit" or not self.lowered_copy:
+        if self.mode == "implicit" or not self.lowered_copy or (self.mode == "strided" and self.first):
             return 0
         n = self.out_shape[0] * self.oh * self.ow
         return n * self.kpad
@@ -174,6 +180,8 @@ class Conv2d(Layer):
                 F.conv_halo_fprop(x, w.view(self.cout, self.k, self.k, self.cin), out=self.y, bias=bias, bn_stats=stats)
             else:
                 F.conv_fprop(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, out=self.y, bias=bias)
+        elif self.mode == "strided":
+            F.conv_fprop_strided(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, stride=self.stride, out=self.y, bias=bias)
         elif self.mode == "lowered":
             col = self._col(x)
             wmat = self.w_pad if self.kpad != self.kdim else w.view(self.cout, self.kdim)
@@ -215,6 +223,9 @@ class Conv2d(Layer):
                 F.conv_halo_wgrad(x, dy, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
             else:
                 F.conv_wgrad(x, dy, R=self.k, S=self.k, pad=self.pad, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
+        elif self.mode == "strided":
+            F.conv_wgrad_strided(x, dy, R=self.k, S=self.k, pad=self.pad, stride=self.stride,
+                                 out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
         elif self.mode == "lowered":
             col = self._col(x, reuse=True)
             if self.kpad != self.kdim:
@@ -240,7 +251,7 @@ class Conv2d(Layer):
             else:
                 F.conv_fprop(dy, self.w_t, pad=self.pad, out=self.dx, residual=dx_residual)
             return self.dx
-        if self.mode == "lowered":
+        if self.mode in ("lowered", "strided"):
             wmat = self.w_pad if self.kpad != self.kdim else self.weight.w.view(self.cout, self.kdim)
             if not self.lowered_copy:
                 F.gemm(dy2, wmat, b_mn_major=True, M=m, N=self.cin, K=self.cout, out=self.dx.view(-1, self.cin),

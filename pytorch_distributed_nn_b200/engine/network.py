@@ -59,6 +59,7 @@ class Network:
         # the epilogue warps the bottleneck: 168 us vs 81 us + 19 us for the separate pass), so it is opt-in
         self.fuse_bn_stats = os.environ.get("PDNN_BN_FUSE") == "1"
         self.bn_mask_from_x = os.environ.get("PDNN_BN_MASK_FROM_X", "1") == "1"   # BN backward without re-reading y (no residual)
+        self.use_strided = os.environ.get("PDNN_NO_STRIDED") != "1"   # stride-2 convs as implicit GEMM (TMA element strides)
         self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
 
     # ---- construction ---------------------------------------------------------------------------

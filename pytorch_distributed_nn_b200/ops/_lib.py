@@ -68,6 +68,8 @@ _P, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint32
 _SIGS = {
     "pdnn_gemm_bf16": [_P, _I, _L, _P, _I, _L, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
     "pdnn_conv_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
+    "pdnn_conv_fprop_strided_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
+    "pdnn_conv_wgrad_strided_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
     "pdnn_conv_halo_supported": [_I] * 8,
     "pdnn_conv_halo_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_fprop_stats_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P, _P],

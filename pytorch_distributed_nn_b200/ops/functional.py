@@ -80,6 +80,29 @@ def conv_fprop(x, w, *, pad, out=None, bias=None, relu=False, residual=None, out
     return out
 
 
+def conv_fprop_strided(x, w, *, pad, stride, out=None, bias=None, relu=False):
+    """Strided conv forward as implicit GEMM (TMA element strides, no im2col). x [N,H,W,C], w [Kout,R,S,C]."""
+    n, h, wd, c = x.shape
+    kout, r, s, _ = w.shape
+    oh, ow = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
+    if out is None:
+        out = torch.empty(n, oh, ow, kout, device=x.device, dtype=BF16)
+    e = _epi(out, kout, 0, relu, 1.0, bias, None)
+    call("pdnn_conv_fprop_strided_bf16", x, w, n, h, wd, c, kout, r, s, pad, stride, C.byref(e), stream_ptr())
+    return out
+
+
+def conv_wgrad_strided(x, dy, *, R, S, pad, stride, out=None, k_splits=0):
+    """dw[Kout,R,S,C] (fp32) += weight gradient of the strided conv; out must be zero-filled."""
+    n, h, wd, c = x.shape
+    kout = dy.shape[-1]
+    if out is None:
+        out = torch.zeros(kout, R, S, c, device=x.device, dtype=F32)
+    e = _epi(out, R * S * c, 2)
+    call("pdnn_conv_wgrad_strided_bf16", x, dy, n, h, wd, c, kout, R, S, pad, stride, C.byref(e), k_splits, stream_ptr())
+    return out
+
+
 def conv_halo_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
     n, h, w, c = x_shape
     return bool(_lib.lib().pdnn_conv_halo_supported(n, h, w, c, kout, R, S, pad))
