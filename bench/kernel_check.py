@@ -252,6 +252,12 @@ def conv_strided():
         yr.backward(dy.float().permute(0, 3, 1, 2))
         dw = F.conv_wgrad_strided(x, dy, R=r, S=r, pad=pad, stride=2)
         ok &= report(f"conv_s2_wgrad[n{n} {h}x{h} c{c} k{k} r{r}]", rel_err(dw, wr.grad.permute(0, 2, 3, 1)), 5e-3)
+        xg = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+        torch.nn.functional.conv2d(xg, w.float().permute(0, 3, 1, 2), stride=2, padding=pad).backward(dy.float().permute(0, 3, 1, 2))
+        res = torch.randn(x.shape, device="cuda").bfloat16() if r == 3 else None     # the 1x1 form writes a quarter of dx
+        dx = F.conv_dgrad_s2(dy, F.wgt_flip_transpose(w), R=r, S=r, pad=pad, residual=res)
+        ref_dx = xg.grad.permute(0, 2, 3, 1) + (res.float() if res is not None else 0)
+        ok &= report(f"conv_s2_dgrad[n{n} {h}x{h} c{c} k{k} r{r}]", rel_err(dx, ref_dx), 1.5e-2)
     return ok
 
 

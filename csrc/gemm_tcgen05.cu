@@ -38,6 +38,12 @@ struct GemmParams {
     // geometry of the activation operand in the conv modes
     int H, W, C, R, S, pad;   // H, W: OUTPUT map (tile decode); the activation tensor map carries the input geometry
     int stride;               // conv stride (1 or 2): the TMA box walks the input with this element stride
+    // tap-list mode (stride-2 dgrad by output parity): k-iteration = (tap t, 64-channel block); A box shifted by
+    // (tap_dh[t], tap_dw[t]) pixels, B columns start at tap_koff[t]
+    int ntaps;
+    int tap_dh[4], tap_dw[4], tap_koff[4];
+    // output row remap of the same mode: tile row (n, i, j) of the dy map -> dx pixel (n, 2i + par_a, 2j + par_b)
+    int out_remap, par_a, par_b;
     int box_h, box_n;        // pixel box (box_w == W)
     int cblks;               // C / 64 (OP_CONVK) or C / BN (OP_CONVMN)
     // epilogue
@@ -161,13 +167,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     } else if (AMODE == OP_CONVK) {
                         const int rs = kit / p.cblks;
                         const int cb = kit - rs * p.cblks;
-                        const int r = rs / p.S;
-                        const int s = rs - r * p.S;
-                        tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
+                        if (p.ntaps > 0) {
+                            tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, p.tap_dw[rs], a_h0 + p.tap_dh[rs], a_n0);
+                        } else {
+                            const int r = rs / p.S;
+                            const int s = rs - r * p.S;
+                            tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
+                        }
                     }
                     // ---- B ----
                     if (BMODE == OP_K2D) {
-                        tma_load_2d(sb, &tmB, fb, kit * BLOCK_K, nt * BN);
+                        int kcol = kit * BLOCK_K;
+                        if (AMODE == OP_CONVK && p.ntaps > 0) {
+                            const int t = kit / p.cblks;
+                            kcol = p.tap_koff[t] + (kit - t * p.cblks) * BLOCK_K;
+                        }
+                        tma_load_2d(sb, &tmB, fb, kcol, nt * BN);
                     } else if (BMODE == OP_MN2D) {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
@@ -248,8 +263,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int mt = rest / p.n_tiles;
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
-            const long long row = (long long)mt * BLOCK_M + ew * 32 + lane;
+            long long row = (long long)mt * BLOCK_M + ew * 32 + lane;
             const bool row_ok = row < p.M;
+            if (p.out_remap) {   // (n, i, j) on the dy map -> dx pixel (n, 2i + a, 2j + b)
+                const int hw_o = p.H * p.W;
+                const int n_ = (int)(row / hw_o);
+                const int rem = (int)(row - (long long)n_ * hw_o);
+                const int i_ = rem / p.W, j_ = rem - i_ * p.W;
+                row = ((long long)n_ * (2 * p.H) + 2 * i_ + p.par_a) * (2 * p.W) + 2 * j_ + p.par_b;
+            }
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 uint32_t v[32];
@@ -702,4 +724,72 @@ extern "C" int pdnn_conv_wgrad_strided_bf16(const void* x, const void* dy, int b
     finish_splits(p);
     if (g3) return launch_gemm<OP_MN2D, OP_CONVMN_G3, 192>(tmA, tmB, p, epi->max_ctas, stream);
     return dispatch_bn<OP_MN2D, OP_CONVMN>(bn, tmA, tmB, p, epi->max_ctas, stream);
+}
+
+
+// Data gradient of a stride-2 convolution without a col2im pass. For stride 2 every input pixel (2i+a, 2j+b) receives
+// contributions only from the filter taps whose parity matches (a, b): four small stride-1 convolutions over dy, one per
+// output parity class, each with 1, 2, 2 or 4 taps, written to the interleaved positions of dx. wt is the
+// pdnn_wgt_flip_transpose()d filter bank [C][R][S][Kout] (tap (r, s) sits at ((R-1-r)*S + (S-1-s)) * Kout).
+// dy: [batch][OH][OW][Kout], dx: [batch][2*OH][2*OW][C]. R = S = 3 (pad 1) or R = S = 1 (pad 0).
+extern "C" int pdnn_conv_dgrad_s2_bf16(const void* dy, const void* wt, int batch, int OH, int OW, int Kout, int C, int R, int S,
+                                       int pad, const pdnn_epilogue_t* epi, void* stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    PDNN_REQUIRE(Kout % 64 == 0, "conv_dgrad_s2: Kout=%d must be a multiple of 64", Kout);
+    PDNN_REQUIRE((R == 3 && S == 3 && pad == 1) || (R == 1 && S == 1 && pad == 0), "conv_dgrad_s2: 3x3/pad1 or 1x1/pad0 only");
+    PDNN_REQUIRE(epi != nullptr && epi->out != nullptr && epi->out_mode == 0, "conv_dgrad_s2: bf16 output required");
+    GemmParams base{};
+    base.stride = 1;
+    PDNN_REQUIRE(pixel_box(OH, OW, batch, BLOCK_M, &base.box_h, &base.box_n) == 0,
+                 "conv_dgrad_s2: %dx%d maps (batch %d) do not tile into 128-pixel boxes", OH, OW, batch);
+    const long long Mll = (long long)batch * OH * OW;
+    PDNN_REQUIRE(Mll % BLOCK_M == 0 && Mll < (1ll << 31), "conv_dgrad_s2: pixel count must be a multiple of 128");
+    const int bn = pick_bn(C);
+    CUtensorMap tmA, tmB;
+    {
+        long long dims[4] = {Kout, OW, OH, batch};
+        long long str[4] = {1, Kout, (long long)OW * Kout, (long long)OH * OW * Kout};
+        int box[4] = {64, OW, base.box_h, base.box_n};
+        if (int rc = make_tmap_bf16(&tmA, dy, 4, dims, str, box)) return rc;
+        long long wd[2] = {(long long)R * S * Kout, C};
+        long long ws[2] = {1, (long long)R * S * Kout};
+        int wb[2] = {64, bn};
+        if (int rc = make_tmap_bf16(&tmB, wt, 2, wd, ws, wb)) return rc;
+    }
+    if (R == 1) {
+        PDNN_REQUIRE(epi->residual == nullptr, "conv_dgrad_s2: a residual is only supported for the 3x3 form (every pixel is written)");
+        // only the (even, even) pixels receive a gradient: everything else is zero
+        PDNN_CUDA_CHECK(cudaMemsetAsync(epi->out, 0, sizeof(__nv_bfloat16) * (size_t)batch * 2 * OH * 2 * OW * (size_t)epi->ldo, stream));
+    }
+    for (int a = 0; a < 2; ++a) {
+        for (int b = 0; b < 2; ++b) {
+            GemmParams p = base;
+            // taps of parity (a, b): h = 2*oh + r - pad  =>  oh = i + (a + pad - r) / 2 for h = 2i + a
+            int nt = 0;
+            for (int r = 0; r < R; ++r) {
+                if (((a + pad - r) & 1) != 0) continue;
+                for (int s2 = 0; s2 < S; ++s2) {
+                    if (((b + pad - s2) & 1) != 0) continue;
+                    p.tap_dh[nt] = (a + pad - r) / 2;
+                    p.tap_dw[nt] = (b + pad - s2) / 2;
+                    p.tap_koff[nt] = ((R - 1 - r) * S + (S - 1 - s2)) * Kout;
+                    ++nt;
+                }
+            }
+            if (nt == 0) continue;
+            p.ntaps = nt;
+            p.M = (int)Mll; p.N = C; p.K = nt * Kout;
+            p.m_tiles = p.M / BLOCK_M;
+            p.n_tiles = (C + bn - 1) / bn;
+            p.cblks = Kout / 64;
+            p.k_iters_total = nt * p.cblks;
+            p.k_splits = 1;
+            finish_splits(p);
+            p.H = OH; p.W = OW; p.C = Kout; p.R = R; p.S = S; p.pad = pad;
+            fill_epilogue(p, epi);
+            p.out_remap = 1; p.par_a = a; p.par_b = b;
+            if (int rc = dispatch_bn<OP_CONVK, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream)) return rc;
+        }
+    }
+    return 0;
 }

@@ -86,6 +86,12 @@ int pdnn_conv_fprop_strided_bf16(const void* x, const void* wgt, int batch, int 
 int pdnn_conv_wgrad_strided_bf16(const void* x, const void* dy, int batch, int H, int W, int C, int Kout, int R, int S,
                                  int pad, int stride, const pdnn_epilogue_t* epi, int k_splits, void* stream);
 
+/* Data gradient of a stride-2 conv (3x3 pad 1 or 1x1 pad 0) without a col2im pass: four parity-class implicit GEMMs
+ * over dy [batch][OH][OW][Kout] write the interleaved pixels of dx [batch][2 OH][2 OW][C]; wt is the
+ * pdnn_wgt_flip_transpose()d filter bank. epi: bf16 out = dx, ldo = C, optional residual (added at dx's pixels). */
+int pdnn_conv_dgrad_s2_bf16(const void* dy, const void* wt, int batch, int OH, int OW, int Kout, int C, int R, int S,
+                            int pad, const pdnn_epilogue_t* epi, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Layer kernels (csrc/nn_kernels.cu)
  * ------------------------------------------------------------------------------------------- */

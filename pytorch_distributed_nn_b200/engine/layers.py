@@ -127,8 +127,12 @@ class Conv2d(Layer):
         elif self.mode == "simt":
             self.kpad = self.kdim
             self.lowered_copy = True
-        if self.mode == "implicit" and not first:
+        if self.mode in ("implicit", "strided") and not first:
             self.w_t = torch.empty(cin, k, k, cout, device=dev, dtype=dt)
+        # stride-2 dgrad by output parity classes (no dcol GEMM + col2im) for the 3x3/pad1 and 1x1/pad0 forms
+        self.parity_dgrad = (self.mode == "strided" and not first and cout % 64 == 0 and h == 2 * self.oh and w == 2 * self.ow
+                             and ((k == 3 and pad == 1) or (k == 1 and pad == 0)) and self._tileable(n, self.oh, self.ow)
+                             and os.environ.get("PDNN_NO_PARITY_DGRAD") != "1")
         self.x = None
         self._colbuf = None
 
@@ -150,13 +154,13 @@ class Conv2d(Layer):
         return [self.weight] + ([self.bias] if self.bias is not None else [])
 
     def scratch_elems(self):
-        if self.mode == "implicit" or not self.lowered_copy or (self.mode == "strided" and self.first):
+        if self.mode == "implicit" or not self.lowered_copy or (self.mode == "strided" and (self.first or self.parity_dgrad)):
             return 0
         n = self.out_shape[0] * self.oh * self.ow
         return n * self.kpad
 
     def prepare(self, net):
-        if self.mode == "implicit" and not self.first:
+        if self.mode in ("implicit", "strided") and not self.first:
             F.wgt_flip_transpose(self.weight.w.view(self.cout, self.k, self.k, self.cin), out=self.w_t)
         elif self.mode == "lowered" and self.kpad != self.kdim:
             self.w_pad[:, : self.kdim].copy_(self.weight.w.view(self.cout, self.kdim))
@@ -250,6 +254,13 @@ class Conv2d(Layer):
                 F.conv_halo_fprop(dy, self.w_t, out=self.dx, residual=dx_residual)
             else:
                 F.conv_fprop(dy, self.w_t, pad=self.pad, out=self.dx, residual=dx_residual)
+            return self.dx
+        if self.mode == "strided" and self.parity_dgrad:
+            if self.k == 1 and dx_residual is not None:
+                F.conv_dgrad_s2(dy, self.w_t, R=1, S=1, pad=0, out=self.dx)
+                F.add(self.dx, dx_residual, out=self.dx)
+            else:
+                F.conv_dgrad_s2(dy, self.w_t, R=self.k, S=self.k, pad=self.pad, out=self.dx, residual=dx_residual)
             return self.dx
         if self.mode in ("lowered", "strided"):
             wmat = self.w_pad if self.kpad != self.kdim else self.weight.w.view(self.cout, self.kdim)

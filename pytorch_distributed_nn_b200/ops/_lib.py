@@ -70,6 +70,7 @@ _SIGS = {
     "pdnn_conv_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_fprop_strided_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_wgrad_strided_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
+    "pdnn_conv_dgrad_s2_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_supported": [_I] * 8,
     "pdnn_conv_halo_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_fprop_stats_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P, _P],

@@ -103,6 +103,18 @@ def conv_wgrad_strided(x, dy, *, R, S, pad, stride, out=None, k_splits=0):
     return out
 
 
+def conv_dgrad_s2(dy, wt, *, R, S, pad, out=None, residual=None):
+    """dx of a stride-2 conv by output parity classes (no col2im). dy [N,OH,OW,Kout], wt = wgt_flip_transpose(w)
+    [C,R,S,Kout] -> dx [N,2*OH,2*OW,C]."""
+    n, oh, ow, kout = dy.shape
+    c = wt.shape[0]
+    if out is None:
+        out = torch.empty(n, 2 * oh, 2 * ow, c, device=dy.device, dtype=BF16)
+    e = _epi(out, c, 0, False, 1.0, None, residual)
+    call("pdnn_conv_dgrad_s2_bf16", dy, wt, n, oh, ow, kout, c, R, S, pad, C.byref(e), stream_ptr())
+    return out
+
+
 def conv_halo_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
     n, h, w, c = x_shape
     return bool(_lib.lib().pdnn_conv_halo_supported(n, h, w, c, kout, R, S, pad))
