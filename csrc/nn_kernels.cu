@@ -28,6 +28,16 @@ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
     float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
     f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
+// raw 16-byte forms: the BatchNorm passes issue a batch of these before touching any of them, so that every
+// thread keeps several loads in flight (one load per thread leaves HBM3e half idle at 1-2 K threads per SM)
+__device__ __forceinline__ uint4 ldg16(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+#ifndef PDNN_BN_UNROLL
+#define PDNN_BN_UNROLL 4
+#endif
 __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
     uint4 u;
     u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
@@ -269,27 +279,46 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
                 (void)sc[j]; (void)sf[j];
             }
         }
-        for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += (long long)gridDim.x * rpi) {
-            const long long off = row * C + ct * 8;
-            float xv[8];
-            load8(x + off, xv);
-            if (MODE == 0) {
+        constexpr int U = PDNN_BN_UNROLL;
+        const long long rstride = (long long)gridDim.x * rpi;
+        const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+        for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride * U) {
+            uint4 rx[U], rd[U], ry[U];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
-            } else {
-                float dv[8];
-                load8(dy + off, dv);
-                if (mask_from_x) {
+            for (int u = 0; u < U; ++u) {
+                // rows past the end re-read the last row (an unconditional load keeps the whole batch in one basic
+                // block, so all of them are issued before the first use) and are zeroed afterwards
+                const long long r = row + u * rstride;
+                const long long off = (r < M ? r : M - 1) * C + ct * 8;
+                rx[u] = ldg16(x + off);
+                if (MODE >= 1) rd[u] = ldg16(dy + off);
+                if (MODE == 1 && relu) ry[u] = ldg16(y + off);
+            }
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) if (!(xv[j] * sc[j] + sf[j] > 0.f)) dv[j] = 0.f;
-                } else if (relu) {
-                    float yv[8];
-                    load8(y + off, yv);
+            for (int u = 1; u < U; ++u)
+                if (row + u * rstride >= M) { if (MODE == 0) rx[u] = zero4; else rd[u] = zero4; }   // a zero x / dy row adds nothing
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+            for (int u = 0; u < U; ++u) {
+                float xv[8];
+                unpack8(rx[u], xv);
+                if (MODE == 0) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { a0[j] += xv[j]; a1[j] += xv[j] * xv[j]; }
+                } else {
+                    float dv[8];
+                    unpack8(rd[u], dv);
+                    if (mask_from_x) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) if (!(xv[j] * sc[j] + sf[j] > 0.f)) dv[j] = 0.f;
+                    } else if (relu) {
+                        float yv[8];
+                        unpack8(ry[u], yv);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { a0[j] += dv[j]; a1[j] += dv[j] * (xv[j] - mean[j]) * inv[j]; }
                 }
-#pragma unroll
-                for (int j = 0; j < 8; ++j) { a0[j] += dv[j]; a1[j] += dv[j] * (xv[j] - mean[j]) * inv[j]; }
             }
         }
         float* s0 = sh + (long long)rgrp * C + ct * 8;
@@ -338,24 +367,37 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const __nv_bfloat16* 
             }
         }
     }
+    constexpr int U = PDNN_BN_UNROLL;
     const long long rstride = (long long)gridDim.x * rpi;
-    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride) {
-        const long long off = row * C + ct * 8;
-        float v[8];
-        load8(x + off, v);
+    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride * U) {
+        uint4 rx[U], rr[U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = v[j] * sc[j] + sf[j];
-        if (residual != nullptr) {
-            float r[8];
-            load8(residual + off, r);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += r[j];
+        for (int u = 0; u < U; ++u) {
+            const long long r = row + u * rstride;
+            const long long off = (r < M ? r : M - 1) * C + ct * 8;     // clamped, unconditional: see bn_reduce_kernel
+            rx[u] = ldg16(x + off);
+            if (residual != nullptr) rr[u] = ldg16(residual + off);
         }
-        if (relu) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        for (int u = 0; u < U; ++u) {
+            const long long r = row + u * rstride;
+            if (r >= M) break;
+            float v[8];
+            unpack8(rx[u], v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = v[j] * sc[j] + sf[j];
+            if (residual != nullptr) {
+                float q[8];
+                unpack8(rr[u], q);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] += q[j];
+            }
+            if (relu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            store8(y + r * C + ct * 8, v);
         }
-        store8(y + off, v);
     }
 }
 
@@ -385,26 +427,42 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
         kc[j] = -ka[j] * s0 * invM - kb[j] * mean;
         if (blockIdx.x == 0 && rgrp == 0) { dgamma[c] = s1; dbeta[c] = s0; }
     }
+    constexpr int U = PDNN_BN_UNROLL;
     const long long rstride = (long long)gridDim.x * rpi;
-    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride) {
-        const long long off = row * C + ct * 8;
-        float xv[8], dv[8];
-        load8(x + off, xv);
-        load8(dy + off, dv);
-        if (mask_from_x) {
+    const bool need_y = relu && !mask_from_x;
+    for (long long row = (long long)blockIdx.x * rpi + rgrp; row < M; row += rstride * U) {
+        uint4 rx[U], rd[U], ry[U];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) if (!(xv[j] * ka[j] + sf[j] > 0.f)) dv[j] = 0.f;
-        } else if (relu) {
-            float yv[8];
-            load8(y + off, yv);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+        for (int u = 0; u < U; ++u) {
+            const long long r = row + u * rstride;
+            const long long off = (r < M ? r : M - 1) * C + ct * 8;     // clamped, unconditional: see bn_reduce_kernel
+            rx[u] = ldg16(x + off);
+            rd[u] = ldg16(dy + off);
+            if (need_y) ry[u] = ldg16(y + off);
         }
-        if (dres != nullptr) store8(dres + off, dv);
-        float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = ka[j] * dv[j] + kb[j] * xv[j] + kc[j];
-        store8(dx + off, o);
+        for (int u = 0; u < U; ++u) {
+            const long long r = row + u * rstride;
+            if (r >= M) break;
+            const long long off = r * C + ct * 8;
+            float xv[8], dv[8];
+            unpack8(rx[u], xv);
+            unpack8(rd[u], dv);
+            if (mask_from_x) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) if (!(xv[j] * ka[j] + sf[j] > 0.f)) dv[j] = 0.f;
+            } else if (relu) {
+                float yv[8];
+                unpack8(ry[u], yv);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) if (!(yv[j] > 0.f)) dv[j] = 0.f;
+            }
+            if (dres != nullptr) store8(dres + off, dv);
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = ka[j] * dv[j] + kb[j] * xv[j] + kc[j];
+            store8(dx + off, o);
+        }
     }
 }
 
@@ -773,6 +831,15 @@ extern "C" int pdnn_col2im_f32(const float* dcol, float* dx, int N, int H, int W
     LAUNCH_OK();
 }
 
+// One resident wave: the BatchNorm passes are grid-stride loops, so a grid larger than what fits on the chip
+// runs as full-length extra waves at partial occupancy (592 blocks at 3 per SM = a second wave on a third of the SMs).
+template <typename K>
+static int resident_blocks(K kernel, int threads, size_t smem) {
+    int per_sm = 0, dev = 0, sms = 148;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return per_sm * sms;
+}
 static int bn_reduce_cfg(int C, int* rpi, size_t* smem) {
     const int tpr = C / 8;
     *rpi = tpr >= 256 ? 1 : 256 / tpr;
@@ -783,7 +850,8 @@ extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
-    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    static const int wave = resident_blocks(bn_reduce_kernel<0>, 256, 16384);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, wave);
     bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
     LAUNCH_OK();
 }
@@ -793,7 +861,8 @@ extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float*
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi_a; size_t smem_a;
     bn_reduce_cfg(C, &rpi_a, &smem_a);
-    bn_fwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
+    static const int wave = resident_blocks(bn_fwd_apply_kernel, 256, 0);
+    bn_fwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
                                                                                      running_mean, running_var, M, C, eps, momentum, relu);
     LAUNCH_OK();
 }
@@ -803,7 +872,8 @@ extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, 
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
-    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    static const int wave1 = resident_blocks(bn_reduce_kernel<1>, 256, 16384), wave2 = resident_blocks(bn_reduce_kernel<2>, 256, 16384);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, (relu && y == nullptr) ? wave2 : wave1);
     if (relu && y == nullptr)
         bn_reduce_kernel<2><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
     else
@@ -817,7 +887,8 @@ extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, c
     PDNN_REQUIRE(C % 8 == 0 && C <= 2048, "bn: C=%d must be a multiple of 8 and <= 2048", C);
     int rpi_a; size_t smem_a;
     bn_reduce_cfg(C, &rpi_a, &smem_a);
-    bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, 148 * 8), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
+    static const int wave = resident_blocks(bn_bwd_apply_kernel, 256, 0);
+    bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
                                                                                      BF(dresidual), dgamma, dbeta, M, C, relu, beta);
     LAUNCH_OK();
 }
@@ -997,7 +1068,8 @@ extern "C" int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const floa
     PDNN_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)C, ST(stream)));
     int rpi; size_t smem;
     bn_reduce_cfg(C, &rpi, &smem);
-    const int grid = grid_for((M + rpi - 1) / rpi, 1, 148 * 4);
+    static const int wave = resident_blocks(bn_reduce_kernel<0>, 256, 16384);
+    const int grid = grid_for((M + rpi - 1) / rpi, 1, wave);
     bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());

@@ -12,7 +12,8 @@ import threading
 
 import torch
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libpdnn_b200.so")
+# PDNN_B200_LIB points at another build of the same library (A/B runs of a kernel variant); default: the in-tree build
+_LIB_PATH = os.environ.get("PDNN_B200_LIB") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lib", "libpdnn_b200.so")
 _lib = None
 _lock = threading.Lock()
 
