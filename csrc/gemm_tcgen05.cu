@@ -299,9 +299,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const bool vec = full && ((p.ldo & 7) == 0);
                     if (p.residual != nullptr) {
                         const __nv_bfloat16* rp = p.residual + row * p.ldo + col0;
+                        if (vec) {   // four 16-byte loads, all issued before the first use
+                            uint4 rq[4];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (full || col0 + i < p.N) f[i] += __bfloat162float(rp[i]);
+                            for (int q = 0; q < 4; ++q) rq[q] = __ldg(reinterpret_cast<const uint4*>(rp) + q);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const float2 r0 = unpack_bf16x2(rq[q].x), r1 = unpack_bf16x2(rq[q].y);
+                                const float2 r2 = unpack_bf16x2(rq[q].z), r3 = unpack_bf16x2(rq[q].w);
+                                f[q * 8 + 0] += r0.x; f[q * 8 + 1] += r0.y; f[q * 8 + 2] += r1.x; f[q * 8 + 3] += r1.y;
+                                f[q * 8 + 4] += r2.x; f[q * 8 + 5] += r2.y; f[q * 8 + 6] += r3.x; f[q * 8 + 7] += r3.y;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (full || col0 + i < p.N) f[i] += __bfloat162float(rp[i]);
+                        }
                     }
                     if (p.relu) {
 #pragma unroll
