@@ -291,6 +291,19 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&h);
 }
+// 256-bit global accesses (sm_100+): one full 32-byte sector per thread and instruction. The epilogues hold one
+// output row per thread; with 16-byte stores every sector was written as two masked halves (2x L1->L2 traffic).
+struct __align__(32) u32x8 { uint32_t v[8]; };
+__device__ __forceinline__ void st_global_256(void* p, const u32x8& r) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r.v[0]), "r"(r.v[1]), "r"(r.v[2]), "r"(r.v[3]),
+                 "r"(r.v[4]), "r"(r.v[5]), "r"(r.v[6]), "r"(r.v[7]) : "memory");
+}
+__device__ __forceinline__ u32x8 ld_global_nc_256(const void* p) {
+    u32x8 r;
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]),
+                 "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]) : "l"(p));
+    return r;
+}
 __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
     __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&u);
     return __bfloat1622float2(h);

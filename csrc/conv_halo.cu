@@ -216,29 +216,29 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                         for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + col0 + i);
                     }
                     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.ldo + col0;
+                    // 32-byte accesses: one full sector per thread and instruction (ldo % 16 == 0 and 32-byte aligned
+                    // bases are checked on the host)
                     if (p.residual != nullptr) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + pix * p.ldo + col0);
+                        const __nv_bfloat16* rp = p.residual + pix * p.ldo + col0;
+                        const u32x8 r0 = ld_global_nc_256(rp), r1 = ld_global_nc_256(rp + 16);
 #pragma unroll
-                        for (int q4 = 0; q4 < 4; ++q4) {
-                            const uint4 u = rp[q4];
-                            float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-                            f[q4 * 8 + 0] += a.x; f[q4 * 8 + 1] += a.y; f[q4 * 8 + 2] += b.x; f[q4 * 8 + 3] += b.y;
-                            f[q4 * 8 + 4] += cc.x; f[q4 * 8 + 5] += cc.y; f[q4 * 8 + 6] += d.x; f[q4 * 8 + 7] += d.y;
+                        for (int q4 = 0; q4 < 8; ++q4) {
+                            const float2 a = unpack_bf16x2(r0.v[q4]), b = unpack_bf16x2(r1.v[q4]);
+                            f[q4 * 2] += a.x; f[q4 * 2 + 1] += a.y; f[16 + q4 * 2] += b.x; f[16 + q4 * 2 + 1] += b.y;
                         }
                     }
                     if (p.relu) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
                     }
+                    u32x8 w0, w1;
 #pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4) {
-                        uint4 w;
-                        w.x = pack_bf16x2(f[q4 * 8 + 0], f[q4 * 8 + 1]);
-                        w.y = pack_bf16x2(f[q4 * 8 + 2], f[q4 * 8 + 3]);
-                        w.z = pack_bf16x2(f[q4 * 8 + 4], f[q4 * 8 + 5]);
-                        w.w = pack_bf16x2(f[q4 * 8 + 6], f[q4 * 8 + 7]);
-                        *reinterpret_cast<uint4*>(o + q4 * 8) = w;
+                    for (int q4 = 0; q4 < 8; ++q4) {
+                        w0.v[q4] = pack_bf16x2(f[q4 * 2], f[q4 * 2 + 1]);
+                        w1.v[q4] = pack_bf16x2(f[16 + q4 * 2], f[16 + q4 * 2 + 1]);
                     }
+                    st_global_256(o, w0);
+                    st_global_256(o + 16, w1);
                 }
                 if (p.bn_stats != nullptr) {
                     // statistics of exactly what was stored (bf16-rounded); positions on the padding columns count as 0
@@ -300,7 +300,9 @@ static int conv_halo_fprop_impl(const void* x, const void* wgt, int batch, int H
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     PDNN_REQUIRE(pdnn_conv_halo_supported(batch, H, W, C, Kout, 3, 3, 1), "conv_halo: unsupported geometry (C=%d Kout=%d %dx%d)", C, Kout, H, W);
     PDNN_REQUIRE(epi != nullptr && epi->out != nullptr && epi->out_mode == 0, "conv_halo: bf16 output required");
-    PDNN_REQUIRE(epi->ldo % 8 == 0, "conv_halo: ldo must be a multiple of 8");
+    PDNN_REQUIRE(epi->ldo % 16 == 0 && (reinterpret_cast<uintptr_t>(epi->out) & 31) == 0 &&
+                     (reinterpret_cast<uintptr_t>(epi->residual) & 31) == 0,
+                 "conv_halo: ldo must be a multiple of 16 and out / residual 32-byte aligned (32-byte epilogue stores)");
     HaloParams p{};
     p.batch = batch; p.H = H; p.W = W; p.C = C; p.Kout = Kout;
     p.Wp = W + 2;

@@ -297,9 +297,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if (p.out_mode == 0) {
                     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + row * p.ldo + col0;
                     const bool vec = full && ((p.ldo & 7) == 0);
+                    // 32-byte form: rows and both base pointers on 32-byte boundaries (CTA-uniform)
+                    const bool vec32 = vec && ((p.ldo & 15) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 31) == 0) &&
+                                       ((reinterpret_cast<uintptr_t>(p.residual) & 31) == 0);
                     if (p.residual != nullptr) {
                         const __nv_bfloat16* rp = p.residual + row * p.ldo + col0;
-                        if (vec) {   // four 16-byte loads, all issued before the first use
+                        if (vec32) {   // two 32-byte loads, both issued before the first use
+                            const u32x8 r0 = ld_global_nc_256(rp), r1 = ld_global_nc_256(rp + 16);
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float2 a2 = unpack_bf16x2(r0.v[q]), b2 = unpack_bf16x2(r1.v[q]);
+                                f[q * 2] += a2.x; f[q * 2 + 1] += a2.y; f[16 + q * 2] += b2.x; f[16 + q * 2 + 1] += b2.y;
+                            }
+                        } else if (vec) {
                             uint4 rq[4];
 #pragma unroll
                             for (int q = 0; q < 4; ++q) rq[q] = __ldg(reinterpret_cast<const uint4*>(rp) + q);
@@ -320,7 +330,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                         for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
                     }
-                    if (vec) {
+                    if (vec32) {       // one full 32-byte sector per store
+                        u32x8 w0, w1;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            w0.v[q] = pack_bf16x2(f[q * 2], f[q * 2 + 1]);
+                            w1.v[q] = pack_bf16x2(f[16 + q * 2], f[16 + q * 2 + 1]);
+                        }
+                        st_global_256(o, w0);
+                        st_global_256(o + 16, w1);
+                    } else if (vec) {
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             uint4 w;
@@ -343,7 +362,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                     const bool vec = full && ((p.ldo & 3) == 0);
                     if (p.out_mode == 1) {
-                        if (vec) {
+                        if (vec && ((p.ldo & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 31) == 0)) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                u32x8 w;
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) w.v[i] = __float_as_uint(f[q * 8 + i]);
+                                st_global_256(o + q * 8, w);
+                            }
+                        } else if (vec) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q)
                                 *reinterpret_cast<float4*>(o + q * 4) =

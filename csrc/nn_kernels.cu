@@ -95,6 +95,23 @@ __global__ void wgt_flip_transpose_kernel(const __nv_bfloat16* __restrict__ w, _
     }
 }
 
+// All convolutions of a network in one launch: blockIdx.y picks the layer from a device table of
+// {source offset in the flat weight buffer, destination address, K, R, S, C} (six 64-bit words per layer).
+__global__ void wgt_flip_transpose_multi_kernel(const __nv_bfloat16* __restrict__ w_flat, const long long* __restrict__ table) {
+    const long long* e = table + 6 * blockIdx.y;
+    const __nv_bfloat16* w = w_flat + e[0];
+    __nv_bfloat16* wt = reinterpret_cast<__nv_bfloat16*>(e[1]);
+    const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
+    const long long total = (long long)K * R * S * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i % K);
+        const int s2 = (int)((i / K) % S);
+        const int r2 = (int)((i / ((long long)K * S)) % R);
+        const int c = (int)(i / ((long long)K * S * R));
+        wt[i] = w[(((long long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c];
+    }
+}
+
 __global__ void oihw_krsc_kernel(const float* __restrict__ src, float* __restrict__ dst, int K, int C, int R, int S, int to_krsc) {
     const long long total = (long long)K * C * R * S;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -791,6 +808,12 @@ extern "C" int pdnn_nchw_f32_to_nhwc_f32(const float* x, float* y, int N, int C,
 }
 extern "C" int pdnn_wgt_flip_transpose(const void* w, void* wt, int K, int R, int S, int C, void* stream) {
     wgt_flip_transpose_kernel<<<grid_for((long long)K * R * S * C, 256), 256, 0, ST(stream)>>>(CBF(w), BF(wt), K, R, S, C);
+    LAUNCH_OK();
+}
+extern "C" int pdnn_wgt_flip_transpose_multi(const void* w_flat, const long long* table_dev, int n_layers, int blocks_per_layer, void* stream) {
+    if (n_layers <= 0) return 0;
+    PDNN_REQUIRE(n_layers <= 65535 && blocks_per_layer >= 1, "wgt_flip_transpose_multi: %d layers / %d blocks per layer", n_layers, blocks_per_layer);
+    wgt_flip_transpose_multi_kernel<<<dim3(blocks_per_layer, n_layers), 256, 0, ST(stream)>>>(CBF(w_flat), table_dev);
     LAUNCH_OK();
 }
 extern "C" int pdnn_oihw_to_krsc_f32(const float* src, float* dst, int K, int C, int R, int S, int to_krsc, void* stream) {

@@ -101,6 +101,9 @@ int pdnn_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream
 int pdnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, void* stream);
 /* KRSC bf16 -> [C][R][S][K] with (r,s) mirrored: the filter bank that turns dgrad into fprop. */
 int pdnn_wgt_flip_transpose(const void* w, void* wt, int K, int R, int S, int C, void* stream);
+/* Every convolution of a network in one launch. table_dev: n_layers x 6 int64 on the device =
+ * {element offset of the KRSC weights in w_flat, destination address, K, R, S, C}. */
+int pdnn_wgt_flip_transpose_multi(const void* w_flat, const long long* table_dev, int n_layers, int blocks_per_layer, void* stream);
 /* fp32 OIHW (torch) <-> KRSC (ours). */
 int pdnn_oihw_to_krsc_f32(const float* src, float* dst, int K, int C, int R, int S, int to_krsc, void* stream);
 

@@ -161,6 +161,8 @@ class Conv2d(Layer):
 
     def prepare(self, net):
         if self.mode in ("implicit", "strided") and not self.first:
+            if net.flip_table is not None:
+                return                      # the network mirrors every filter bank in one launch
             F.wgt_flip_transpose(self.weight.w.view(self.cout, self.k, self.k, self.cin), out=self.w_t)
         elif self.mode == "lowered" and self.kpad != self.kdim:
             self.w_pad[:, : self.kdim].copy_(self.weight.w.view(self.cout, self.kdim))
@@ -310,7 +312,8 @@ class BatchNorm(Layer):
         self._had_residual = residual is not None
         F.bn_forward(x, self.weight.wf, self.bias.wf, relu=self.relu, residual=residual, eps=self.eps,
                      momentum=self.momentum, running_mean=self.running_mean, running_var=self.running_var,
-                     stats=self.stats, mean_invstd=self.mean_invstd, out=self.y, stats_ready=self.stats_ready)
+                     stats=self.stats, mean_invstd=self.mean_invstd, out=self.y, stats_ready=self.stats_ready,
+                     prezeroed=self.net.pool_fresh)
         self.stats_ready = False
         return self.y
 
@@ -325,7 +328,7 @@ class BatchNorm(Layer):
         y = self.y if (self._had_residual or not self.relu or not self.net.bn_mask_from_x) else None
         F.bn_backward(self.x, y, dy, self.weight.wf, self.mean_invstd, relu=self.relu,
                       want_dresidual=want_dresidual, sums=self.sums, dx=self.dx, dresidual=self.dres,
-                      dgamma=self.weight.g, dbeta=self.bias.g, beta=self.bias.wf)
+                      dgamma=self.weight.g, dbeta=self.bias.g, beta=self.bias.wf, prezeroed=self.net.pool_fresh)
         self.net.grad_ready(self.bias)
         self.net.grad_ready(self.weight)
         return self.dx, (self.dres if want_dresidual else None)

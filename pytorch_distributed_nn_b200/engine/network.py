@@ -52,6 +52,9 @@ class Network:
         self._param_bucket = {}
         self.loss = torch.zeros(1, device=self.device, dtype=F32)
         self.correct = torch.zeros(1, device=self.device, dtype=torch.int32)
+        self.flip_table = None     # finalize(): device table for the one-launch mirrored-filter pass
+        self.zpool = None          # finalize(): one buffer for everything that must start a step at zero
+        self.pool_fresh = False
         self.dlogits = None
         self.x_in = None
         self.keep_col = True   # keep im2col matrices of lowered convs for backward (memory for time)
@@ -78,6 +81,19 @@ class Network:
                 self.param_list.append(p)
         self.total = off
         dev = self.device
+        # zero pool: [loss, correct, then (stats, sums) of every BatchNorm], 64-float aligned slots
+        bns = [l for l in self._all_layers() if isinstance(l, L.BatchNorm)]
+        zoff = 64
+        for bn in bns:
+            bn._zoff = zoff
+            zoff += (4 * bn.c + 63) // 64 * 64
+        if dev.type != "meta":
+            self.zpool = torch.zeros(zoff, device=dev, dtype=F32)
+            self.loss = self.zpool[0:1]
+            self.correct = self.zpool[1:2].view(torch.int32)
+            for bn in bns:
+                bn.stats = self.zpool[bn._zoff: bn._zoff + 2 * bn.c].view(2, bn.c)
+                bn.sums = self.zpool[bn._zoff + 2 * bn.c: bn._zoff + 4 * bn.c].view(2, bn.c)
         self.w32 = torch.zeros(off, device=dev, dtype=F32)
         self.w = external_w if external_w is not None else torch.zeros(off, device=dev, dtype=self.dtype)
         self.g = external_g if external_g is not None else torch.zeros(off, device=dev, dtype=F32)
@@ -89,6 +105,14 @@ class Network:
             p.g = self.g[p.offset: p.offset + p.numel]
             p.w32 = self.w32[p.offset: p.offset + p.numel]
             p.wf = self.wf[p.offset: p.offset + p.numel]
+        if dev.type == "cuda" and self.w.dtype == BF16:
+            rows = []
+            for l in self._all_layers():
+                if isinstance(l, L.Conv2d) and getattr(l, "w_t", None) is not None and l.mode in ("implicit", "strided") and not l.first:
+                    rows.append([l.weight.offset, l.w_t.data_ptr(), l.cout, l.k, l.k, l.cin])
+            if rows:
+                self._n_flip = len(rows)
+                self.flip_table = torch.tensor(rows, dtype=torch.long).to(dev)
         scratch = 0
         for layer in self.layers:
             if hasattr(layer, "scratch_elems"):
@@ -159,6 +183,8 @@ class Network:
         """Run once per step after new compute weights landed: fp32 shadow + per-layer derived layouts."""
         if self.wf is not self.w:
             F.cast_to_f32(self.w[: self.total], out=self.wf)
+        if self.flip_table is not None:
+            F.wgt_flip_transpose_multi(self.w, self.flip_table, self._n_flip)
         for layer in self.layers:
             layer.prepare(self)
 
@@ -248,6 +274,9 @@ class Network:
     def forward(self, x_nchw_f32):
         x = self.stage_input(x_nchw_f32)
         layers = self.layers
+        if self.zpool is not None:     # BatchNorm sums of both passes, loss and hit counter: one fill per step
+            self.zpool.zero_()
+            self.pool_fresh = True
         for i, layer in enumerate(layers):
             if isinstance(layer, L.Conv2d) and i + 1 < len(layers) and isinstance(layers[i + 1], L.BatchNorm):
                 x = layer.forward(x, bn=layers[i + 1])     # the conv epilogue may produce that BatchNorm's statistics
@@ -257,8 +286,9 @@ class Network:
         return x
 
     def loss_and_grad(self, labels):
-        self.loss.zero_()
-        self.correct.zero_()
+        if not self.pool_fresh:
+            self.loss.zero_()
+            self.correct.zero_()
         F.cross_entropy(self.logits, labels, self.num_classes, loss=self.loss, dlogits=self.dlogits, correct=self.correct)
         return self.loss
 
@@ -266,6 +296,7 @@ class Network:
         dy = self.dlogits
         for layer in reversed(self.layers):
             dy = layer.backward(dy)
+        self.pool_fresh = False
 
     def train_step(self, x_nchw_f32, labels):
         """forward + loss + backward; gradients end up in ``self.g`` (and buckets fire ``on_bucket``)."""

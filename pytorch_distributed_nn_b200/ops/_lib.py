@@ -83,6 +83,7 @@ _SIGS = {
     "pdnn_nchw_f32_to_nhwc_bf16": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_nchw_f32_to_nhwc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_wgt_flip_transpose": [_P, _P, _I, _I, _I, _I, _P],
+    "pdnn_wgt_flip_transpose_multi": [_P, _P, _I, _I, _P],
     "pdnn_oihw_to_krsc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_im2col_bf16": [_P, _P] + [_I] * 11 + [_P],
     "pdnn_im2col_f32": [_P, _P] + [_I] * 11 + [_P],

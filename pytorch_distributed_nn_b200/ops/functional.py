@@ -162,6 +162,11 @@ def conv_wgrad(x, dy, *, R, S, pad, out=None, k_splits=0):
     return out
 
 
+def wgt_flip_transpose_multi(w_flat, table, n_layers, blocks_per_layer=32):
+    """One launch for all mirrored filter banks of a network (see pdnn_wgt_flip_transpose_multi for the table)."""
+    call("pdnn_wgt_flip_transpose_multi", w_flat, table, n_layers, blocks_per_layer, stream_ptr())
+
+
 def wgt_flip_transpose(w, out=None):
     kout, r, s, c = w.shape
     if out is None:
@@ -236,14 +241,15 @@ def col2im(dcol, x_shape, R, S, stride, pad, out=None):
 
 
 def bn_forward(x, gamma, beta, *, relu=False, residual=None, eps=1e-5, momentum=0.1, running_mean=None,
-               running_var=None, stats=None, mean_invstd=None, out=None, stats_ready=False):
+               running_var=None, stats=None, mean_invstd=None, out=None, stats_ready=False, prezeroed=False):
     """Training-mode BatchNorm over all but the last dim of NHWC bf16 x. Returns (y, mean_invstd).
-    ``stats_ready``: ``stats`` already holds sum / sum of squares (produced by the conv epilogue): skip that pass."""
+    ``stats_ready``: ``stats`` already holds sum / sum of squares (produced by the conv epilogue): skip that pass.
+    ``prezeroed``: the caller cleared ``stats`` already (the engine clears one pool per step instead of 2 fills per layer)."""
     c = x.shape[-1]
     m = x.numel() // c
     if stats is None:
         stats = torch.zeros(2, c, device=x.device, dtype=F32)
-    elif not stats_ready:
+    elif not stats_ready and not prezeroed:
         stats.zero_()
     if mean_invstd is None:
         mean_invstd = torch.empty(2, c, device=x.device, dtype=F32)
@@ -258,13 +264,13 @@ def bn_forward(x, gamma, beta, *, relu=False, residual=None, eps=1e-5, momentum=
 
 
 def bn_backward(x, y, dy, gamma, mean_invstd, *, relu=False, want_dresidual=False, sums=None, dx=None,
-                dresidual=None, dgamma=None, dbeta=None, beta=None):
+                dresidual=None, dgamma=None, dbeta=None, beta=None, prezeroed=False):
     """``y=None`` (allowed when the forward had no residual and ``beta`` is given) rebuilds the ReLU mask from x."""
     c = x.shape[-1]
     m = x.numel() // c
     if sums is None:
         sums = torch.zeros(2, c, device=x.device, dtype=F32)
-    else:
+    elif not prezeroed:
         sums.zero_()
     if dx is None:
         dx = torch.empty_like(x)
