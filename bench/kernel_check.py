@@ -195,6 +195,12 @@ def conv_halo():
         out = F.conv_halo_fprop(x, w, bias=bias, residual=res, relu=True)
         ref = torch.relu(_conv_ref(x, w, 1) + bias + res.float())
         ok &= report(f"conv_halo[n{n} {h}x{h} c{c} k{k}]", rel_err(out, ref), 1.5e-2)
+        # BatchNorm statistics from the epilogue: sum and sum of squares of exactly what was stored
+        stats = torch.zeros(2, k, device="cuda")
+        out = F.conv_halo_fprop(x, w, bn_stats=stats)
+        of = out.float().reshape(-1, k)
+        ok &= report(f"conv_halo_stats_sum[n{n} {h}x{h} c{c} k{k}]", rel_err(stats[0], of.sum(0)), 1e-3)
+        ok &= report(f"conv_halo_stats_sq[n{n} {h}x{h} c{c} k{k}]", rel_err(stats[1], (of * of).sum(0)), 1e-3)
     for (n, h, c, k) in [(256, 32, 64, 64), (256, 16, 128, 128)]:
         x = torch.randn(n, h, h, c, device="cuda").bfloat16()
         w = (torch.randn(k, 3, 3, c, device="cuda") / 24).bfloat16()

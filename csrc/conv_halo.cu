@@ -187,9 +187,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     } else if (warp >= 4) {
         const int ew = warp & 3;
         int seq = 0;
-        // BatchNorm statistics of the output, accumulated per lane across all tiles of this CTA (the CTA's 64 output
-        // channels never change), flushed with one atomicAdd per lane and 32-column chunk at the very end
-        float st_sum[HALO_BN / 32] = {0.f, 0.f}, st_sq[HALO_BN / 32] = {0.f, 0.f};
+        // BatchNorm statistics of the output. Every thread keeps private sums for its 64 columns over ALL tiles of this
+        // CTA (the CTA's output channels never change; only the row a thread holds does), so the epilogue pays two FMAs per
+        // element and the cross-lane reduction (31 shuffles per 32 columns) happens once per CTA, not once per tile.
+        float st_sum[HALO_BN / 32][32], st_sq[HALO_BN / 32][32];
+#pragma unroll
+        for (int c = 0; c < HALO_BN / 32; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) { st_sum[c][i] = 0.f; st_sq[c][i] = 0.f; }
         for (int tile = cta_in_cb; tile < total_tiles; tile += ctas_per_cb, ++seq) {
             const int acc = (seq % HALO_ISSUERS) * 2 + ((seq / HALO_ISSUERS) & 1);
             const uint32_t acc_phase = (uint32_t)((seq / HALO_ISSUERS) >> 1) & 1u;
@@ -240,17 +245,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                     st_global_256(o, w0);
                     st_global_256(o + 16, w1);
                 }
-                if (p.bn_stats != nullptr) {
-                    // statistics of exactly what was stored (bf16-rounded); positions on the padding columns count as 0
-                    float s1[32], s2[32];
+                if (p.bn_stats != nullptr && valid) {
+                    // statistics of exactly what was stored (bf16-rounded); the padding columns are not counted
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        const float r = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
-                        s1[i] = r;
-                        s2[i] = r * r;
+                        const float r = __bfloat162float(__float2bfloat16(f[i]));
+                        st_sum[c][i] += r;
+                        st_sq[c][i] = fmaf(r, r, st_sq[c][i]);
                     }
-                    st_sum[c] += warp_column_sums(s1, lane);
-                    st_sq[c] += warp_column_sums(s2, lane);
                 }
             }
             tc_fence_before();
@@ -260,8 +262,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         if (p.bn_stats != nullptr) {
 #pragma unroll
             for (int c = 0; c < HALO_BN / 32; ++c) {
-                atomicAdd(p.bn_stats + cb * HALO_BN + c * 32 + lane, st_sum[c]);
-                atomicAdd(p.bn_stats + p.Kout + cb * HALO_BN + c * 32 + lane, st_sq[c]);
+                const float s1 = warp_column_sums(st_sum[c], lane);
+                const float s2 = warp_column_sums(st_sq[c], lane);
+                atomicAdd(p.bn_stats + cb * HALO_BN + c * 32 + lane, s1);
+                atomicAdd(p.bn_stats + p.Kout + cb * HALO_BN + c * 32 + lane, s2);
             }
         }
     }
