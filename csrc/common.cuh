@@ -118,6 +118,34 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
         ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// ---- thread-block clusters ----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// store one word into the same shared-memory variable of another CTA of the cluster
+__device__ __forceinline__ void st_shared_remote_u32(uint32_t local_saddr, uint32_t cta_rank, uint32_t v) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "st.shared::cluster.u32 [ra], %2;\n\t}\n"
+        ::"r"(local_saddr), "r"(cta_rank), "r"(v)
+        : "memory");
+}
+// TMA tile load delivered to the same shared-memory offset of every CTA in cta_mask; each destination CTA's mbarrier
+// (same offset) receives the complete_tx for the bytes that landed in that CTA.
+__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
+                                                      uint16_t cta_mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "h"(cta_mask)
+        : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c0,
                                             int c1, int c2, int c3) {
     asm volatile(
@@ -187,6 +215,16 @@ __device__ __forceinline__ void umma_commit_pred(uint32_t bar, uint32_t issue) {
         "setp.ne.b32 q, %1, 0;\n\t"
         "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n"
         ::"r"(bar), "r"(issue)
+        : "memory");
+}
+// the same arrival delivered to the mbarrier at this offset in every CTA of cta_mask (stage release in a cluster whose
+// CTAs fill each other's stages by multicast)
+__device__ __forceinline__ void umma_commit_multicast_pred(uint32_t bar, uint16_t cta_mask, uint32_t issue) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %2, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}\n"
+        ::"r"(bar), "h"(cta_mask), "r"(issue)
         : "memory");
 }
 // tcgen05.commit: the mbarrier gets one arrival once every MMA issued so far by this thread retired.

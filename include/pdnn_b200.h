@@ -22,6 +22,8 @@ int pdnn_version(void);
 /* Number of kernel launches issued through this library by the calling process (all threads). */
 long long pdnn_launch_count(void);
 void pdnn_reset_launch_count(void);
+/* Adds n to the counter: called once per CUDA-graph replay with the number of library kernels captured in that graph. */
+void pdnn_add_launch_count(long long n);
 
 /* ---------------------------------------------------------------------------------------------
  * GEMM / convolution on tcgen05 + TMEM + TMA (csrc/gemm_tcgen05.cu)
@@ -52,6 +54,10 @@ int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, 
  * wgt: bf16 [Kout][R][S][C]; out rows are output pixels in NHWC order, ldo >= Kout.
  * Data-gradient of the same conv = this entry point on dy with pdnn_wgt_flip_transpose()'d weights.
  * ref: nn.Conv2d 3x3 fwd / bwd-data (pytorch_code/model_ops/resnet.py:19-21,72; resnet_split.py:28,34). */
+/* Two-CTA cluster schedule of the K-major GEMM / conv fprop kernels (each CTA multicasts half of every B tile into
+ * both): 1 = on, 0 = off (default; env PDNN_CLUSTER=1 turns it on at first use). Returns the previous setting. */
+int pdnn_set_cluster_mode(int on);
+
 int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
                          int R, int S, int pad, const pdnn_epilogue_t* epi, void* stream);
 

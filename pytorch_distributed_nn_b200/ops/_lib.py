@@ -83,6 +83,7 @@ _SIGS = {
     "pdnn_nchw_f32_to_nhwc_bf16": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_nchw_f32_to_nhwc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_wgt_flip_transpose": [_P, _P, _I, _I, _I, _I, _P],
+    "pdnn_set_cluster_mode": [_I],
     "pdnn_wgt_flip_transpose_multi": [_P, _P, _I, _I, _P],
     "pdnn_oihw_to_krsc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_im2col_bf16": [_P, _P] + [_I] * 11 + [_P],
@@ -163,6 +164,8 @@ def lib():
         h.pdnn_last_error.restype = C.c_char_p
         h.pdnn_launch_count.restype = C.c_longlong
         h.pdnn_reset_launch_count.restype = None
+        h.pdnn_add_launch_count.restype = None
+        h.pdnn_add_launch_count.argtypes = [C.c_longlong]
         for name, sig in _SIGS.items():
             fn = getattr(h, name, None)
             if fn is None:
@@ -203,3 +206,8 @@ def launch_count() -> int:
 
 def reset_launch_count() -> None:
     lib().pdnn_reset_launch_count()
+
+
+def add_launch_count(n: int) -> None:
+    """Account for library kernels that ran through a CUDA-graph replay (see pdnn_add_launch_count)."""
+    lib().pdnn_add_launch_count(int(n))

@@ -243,8 +243,10 @@ class B200ParameterServer:
         torch.cuda.synchronize()
         self.step += 1
         self._graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
         with torch.cuda.graph(self._graph):
             self._graph_loss = self._step_body(self._gx, self._gy)
+        self.graph_kernel_launches = _lib.launch_count() - n0      # library kernels inside one replay
         return self
 
     def _step_body(self, x, y):
@@ -262,6 +264,7 @@ class B200ParameterServer:
                 self._gx.copy_(x_nchw_f32, non_blocking=True)
                 self._gy.copy_(labels, non_blocking=True)
             self._graph.replay()
+            _lib.add_launch_count(self.graph_kernel_launches)
             self.step += 1
             return self._graph_loss
         loss = None

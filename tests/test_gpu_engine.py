@@ -220,9 +220,13 @@ def test_cuda_graph_replay_matches_eager_steps():
     b.train_step(x[0], y[0])
     b.train_step(x[1], y[1])
     b.enable_cuda_graph(x[2], y[2])        # runs one real step on its example batch (step 3) and captures
+    from pytorch_distributed_nn_b200.ops import _lib
     b.train_step(x[3], y[3])
+    _lib.reset_launch_count()
     loss = b.train_step(x[4], y[4])
     torch.cuda.synchronize()
+    # a replay runs the captured library kernels without passing the host entry points: the counter still sees them
+    assert b.graph_kernel_launches > 10 and _lib.launch_count() == b.graph_kernel_launches
     assert b.last_result() == (1, 0, 1, 5) and float(loss) == float(loss)
     assert torch.allclose(b.net.w32, wa, rtol=1e-4, atol=1e-5)
     b.close()
