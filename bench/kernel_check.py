@@ -207,6 +207,45 @@ def gemm_cluster():
 
 
 @case
+def conv_stem():
+    """Stem conv (C <= 3 -> 64): output, the im2col by-product and the BatchNorm statistics."""
+    F = _F()
+    ok = True
+    for (n, h, c) in [(8, 32, 3), (4, 16, 3), (2, 8, 3), (16, 8, 1), (8, 16, 2), (300, 32, 3)]:
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        w = (torch.randn(64, 3, 3, c, device="cuda") / (3 * c ** 0.5)).bfloat16()
+        w_pad = torch.zeros(64, 32, device="cuda", dtype=torch.bfloat16)
+        w_pad[:, : 9 * c] = w.reshape(64, -1)
+        col = torch.full((n * h * h, 32), 7.0, device="cuda", dtype=torch.bfloat16)
+        stats = torch.zeros(2, 64, device="cuda")
+        assert F.conv_stem_supported(x.shape, 64)
+        out = F.conv_stem(x, w_pad, col=col, bn_stats=stats)
+        ref = _conv_ref(x, w, 1)
+        ok &= report(f"conv_stem[n{n} {h}x{h} c{c}]", rel_err(out, ref), 1.5e-2)
+        col_ref = F.im2col(x, 3, 3, 1, 1, k_pad=32)
+        ok &= report(f"conv_stem_col[n{n} {h}x{h} c{c}]", rel_err(col, col_ref), 1e-6)
+        of = out.float().reshape(-1, 64)
+        ok &= report(f"conv_stem_stats[n{n} {h}x{h} c{c}]", max(rel_err(stats[0], of.sum(0)), rel_err(stats[1], (of * of).sum(0))), 1e-3)
+        bias = torch.randn(64, device="cuda")
+        out2 = F.conv_stem(x, w_pad, bias=bias, relu=True)
+        ok &= report(f"conv_stem_bias_relu[n{n} {h}x{h} c{c}]", rel_err(out2, torch.relu(ref + bias)), 1.5e-2)
+    x = torch.randn(1024, 32, 32, 3, device="cuda").bfloat16()
+    w_pad = torch.zeros(64, 32, device="cuda", dtype=torch.bfloat16)
+    w_pad[:, :27] = (torch.randn(64, 27, device="cuda") / 5).bfloat16()
+    out = torch.empty(1024, 32, 32, 64, device="cuda", dtype=torch.bfloat16)
+    col = torch.empty(1024 * 32 * 32, 32, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2, 64, device="cuda")
+    ms0 = time_ms(lambda: F.conv_stem(x, w_pad, out=out))
+    ms1 = time_ms(lambda: F.conv_stem(x, w_pad, out=out, col=col, bn_stats=stats))
+    def two_pass():
+        c2 = F.im2col(x, 3, 3, 1, 1, k_pad=32, out=col)
+        F.gemm(c2, w_pad, out=out.view(-1, 64))
+    ms2 = time_ms(two_pass)
+    print(f"PERF conv_stem n1024 32x32 c3: plain {ms0 * 1e3:.1f} us, +col+stats {ms1 * 1e3:.1f} us, im2col+GEMM {ms2 * 1e3:.1f} us", flush=True)
+    return ok
+
+
+@case
 def conv_halo():
     F = _F()
     ok = True

@@ -17,7 +17,7 @@ CSRC = os.path.join(ROOT, "csrc")
 OUT_DIR = os.path.join(ROOT, "pytorch_distributed_nn_b200", "lib")
 OBJ_DIR = os.path.join(ROOT, "build", "obj")
 LIB = os.path.join(OUT_DIR, "libpdnn_b200.so")
-SOURCES = ["core.cu", "gemm_tcgen05.cu", "conv_halo.cu", "nn_kernels.cu", "ps_kernels.cu", "fc_ps_native.cu"]
+SOURCES = ["core.cu", "gemm_tcgen05.cu", "conv_halo.cu", "conv_stem.cu", "nn_kernels.cu", "ps_kernels.cu", "fc_ps_native.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "--expt-relaxed-constexpr",

@@ -54,6 +54,15 @@ int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, const void* B, 
  * wgt: bf16 [Kout][R][S][C]; out rows are output pixels in NHWC order, ldo >= Kout.
  * Data-gradient of the same conv = this entry point on dy with pdnn_wgt_flip_transpose()'d weights.
  * ref: nn.Conv2d 3x3 fwd / bwd-data (pytorch_code/model_ops/resnet.py:19-21,72; resnet_split.py:28,34). */
+/* Stem convolution: 3x3 / stride 1 / pad 1, C <= 3 input channels, 64 output channels (the first layer of the CIFAR
+ * ResNets and VGGs). The im2col rows are built in registers and written straight into the swizzled MMA operand stage;
+ * no im2col pass, no 64-byte-row GEMM. w_pad: [64][32] bf16 (KRSC rows zero-padded from 9*C to 32). col (optional):
+ * receives the [M][32] im2col matrix for the weight-gradient GEMM. bn_stats (optional, [2][64] fp32, zeroed by the
+ * caller): per-channel sum / sum of squares of the stored output. */
+int pdnn_conv_stem_supported(int batch, int H, int W, int C, int Kout, int R, int S, int stride, int pad);
+int pdnn_conv_stem_bf16(const void* x, const void* w_pad, int batch, int H, int W, int C, int Kout,
+                        const pdnn_epilogue_t* epi, void* col, float* bn_stats, void* stream);
+
 /* Two-CTA cluster schedule of the K-major GEMM / conv fprop kernels (each CTA multicasts half of every B tile into
  * both): 1 = on, 0 = off (default; env PDNN_CLUSTER=1 turns it on at first use). Returns the previous setting. */
 int pdnn_set_cluster_mode(int on);

@@ -130,6 +130,9 @@ class Conv2d(Layer):
         elif self.mode == "simt":
             self.kpad = self.kdim
             self.lowered_copy = True
+        # stem (C <= 3 -> 64 channels): im2col rows built in registers inside the conv kernel (conv_stem.cu)
+        self.stem = (self.mode == "lowered" and first and net.device.type == "cuda" and self.kpad == 32
+                     and os.environ.get("PDNN_NO_STEM") != "1" and F.conv_stem_supported(in_shape, cout, k, k, stride, pad))
         if self.mode in ("implicit", "strided") and not first:
             self.w_t = torch.empty(cin, k, k, cout, device=dev, dtype=dt)
         # stride-2 dgrad by output parity classes (no dcol GEMM + col2im) for the 3x3/pad1 and 1x1/pad0 forms
@@ -183,7 +186,8 @@ class Conv2d(Layer):
             if self.halo_f:
                 stats = None
                 if bn is not None and self.net.fuse_bn_stats:
-                    bn.stats.zero_()
+                    if not self.net.pool_fresh:
+                        bn.stats.zero_()
                     bn.stats_ready = True
                     stats = bn.stats
                 F.conv_halo_fprop(x, w.view(self.cout, self.k, self.k, self.cin), out=self.y, bias=bias, bn_stats=stats)
@@ -191,6 +195,19 @@ class Conv2d(Layer):
                 F.conv_fprop(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, out=self.y, bias=bias)
         elif self.mode == "strided":
             F.conv_fprop_strided(x, w.view(self.cout, self.k, self.k, self.cin), pad=self.pad, stride=self.stride, out=self.y, bias=bias)
+        elif self.mode == "lowered" and self.stem:
+            col = None
+            if self.net.keep_col:        # the kernel writes the im2col matrix the weight-gradient GEMM reads as a by-product
+                if self._colbuf is None:
+                    self._colbuf = torch.empty(self.out_shape[0] * self.oh * self.ow, self.kpad, device=self.net.device, dtype=self.net.dtype)
+                col = self._colbuf
+            stats = None
+            if bn is not None and self.net.fuse_bn_stats:
+                if not self.net.pool_fresh:
+                    bn.stats.zero_()
+                bn.stats_ready = True
+                stats = bn.stats
+            F.conv_stem(x, self.w_pad, out=self.y, bias=bias, col=col, bn_stats=stats)
         elif self.mode == "lowered":
             col = self._col(x)
             wmat = self.w_pad if self.kpad != self.kdim else w.view(self.cout, self.kdim)

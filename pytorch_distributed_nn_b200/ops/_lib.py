@@ -73,6 +73,7 @@ _SIGS = {
     "pdnn_conv_wgrad_strided_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _I, _P],
     "pdnn_conv_dgrad_s2_bf16": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_supported": [_I] * 8,
+    "pdnn_conv_stem_supported": [_I] * 9,
     "pdnn_conv_halo_fprop_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P],
     "pdnn_conv_halo_fprop_stats_bf16": [_P, _P, _I, _I, _I, _I, _I, C.POINTER(Epilogue), _P, _P],
     "pdnn_conv_halo_wgrad_supported": [_I] * 8,
@@ -83,6 +84,7 @@ _SIGS = {
     "pdnn_nchw_f32_to_nhwc_bf16": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_nchw_f32_to_nhwc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],
     "pdnn_wgt_flip_transpose": [_P, _P, _I, _I, _I, _I, _P],
+    "pdnn_conv_stem_bf16": [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P],
     "pdnn_set_cluster_mode": [_I],
     "pdnn_wgt_flip_transpose_multi": [_P, _P, _I, _I, _P],
     "pdnn_oihw_to_krsc_f32": [_P, _P, _I, _I, _I, _I, _I, _P],

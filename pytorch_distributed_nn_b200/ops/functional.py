@@ -115,6 +115,24 @@ def conv_dgrad_s2(dy, wt, *, R, S, pad, out=None, residual=None):
     return out
 
 
+def conv_stem_supported(x_shape, kout, R=3, S=3, stride=1, pad=1) -> bool:
+    n, h, w, c = x_shape
+    return bool(_lib.lib().pdnn_conv_stem_supported(n, h, w, c, kout, R, S, stride, pad))
+
+
+def conv_stem(x, w_pad, *, out=None, bias=None, relu=False, col=None, bn_stats=None):
+    """Stem conv (3x3/s1/p1, C <= 3 -> 64 channels): x [N,H,W,C] bf16, w_pad [64,32] bf16 (KRSC rows padded with zeros).
+    ``col`` ([N*H*W, 32] bf16) additionally receives the im2col matrix (for the weight-gradient GEMM); ``bn_stats``
+    ([2,64] fp32, zeroed by the caller) the per-channel sum / sum of squares of the output."""
+    n, h, wd, c = x.shape
+    kout = w_pad.shape[0]
+    if out is None:
+        out = torch.empty(n, h, wd, kout, device=x.device, dtype=BF16)
+    e = _epi(out, kout, 0, relu, 1.0, bias, None)
+    call("pdnn_conv_stem_bf16", x, w_pad, n, h, wd, c, kout, C.byref(e), col, bn_stats, stream_ptr())
+    return out
+
+
 def conv_halo_supported(x_shape, kout, R=3, S=3, pad=1) -> bool:
     n, h, w, c = x_shape
     return bool(_lib.lib().pdnn_conv_halo_supported(n, h, w, c, kout, R, S, pad))
