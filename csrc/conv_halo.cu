@@ -392,6 +392,7 @@ struct HaloWgradParams {
     int n_cin_blocks, n_cout_blocks;
     int dy_bytes, halo_off, stage_bytes, stages;
     int ctas_group_a;      // CTAs working on taps 0..5 ; the rest work on taps 6..8
+    int wide;              // 1: one N = 192 MMA per filter row (three taps through LBO = one pixel); 0: one N = 64 MMA per tap
     float* out;            // [Kout][9 * C] fp32, red.add
     const uint32_t* guard_closed;
     const uint32_t* guard_step;
@@ -502,6 +503,24 @@ conv_halo_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
             const uint32_t sb = smem_base + stage * p.stage_bytes;
             const uint64_t a0 = a_hi_lbo + (uint64_t)((sb & 0x3FFFF) >> 4);
             const uint64_t b0 = b_hi_lbo + (uint64_t)(((sb + p.halo_off) & 0x3FFFF) >> 4);
+            if (p.wide) {
+                // The three taps of a filter row read the halo at shifts -1, 0, +1 pixels = consecutive 128-byte rows of
+                // the MN-major B operand. A descriptor whose 64-wide N chunks are LBO = 128 bytes apart therefore covers all
+                // three in ONE N = 192 MMA: dY (the A operand) is read from shared memory once per filter row instead of
+                // once per tap, which is what bounded the N = 64 form (192 B/clk of operand reads against 128 B/clk).
+                constexpr uint32_t idesc3 = make_idesc_bf16(128, 3 * HALO_BN, 1, 1);
+                const uint64_t b_lbo128 = make_smem_desc_sw128(0, 128, 1024) - b_hi_lbo;      // LBO field only
+                for (int lr = issuer; lr < ntaps / 3; lr += HALO_ISSUERS) {
+                    const int r = tap0 / 3 + lr;
+                    const int shift = r * p.Wp - 1;
+                    const uint32_t tmem_d = tmem_base + lr * 3 * HALO_BN;
+                    const uint64_t b_row = b0 + b_lbo128 + (uint64_t)(int64_t)(shift * 8);
+#pragma unroll 4
+                    for (int k = 0; k < p.KS; ++k) {
+                        umma_bf16_ss_pred(tmem_d, a0 + (uint64_t)(k * 128), b_row + (uint64_t)(k * 128), idesc3, (first && k == 0) ? 0u : 1u, issue);
+                    }
+                }
+            } else
             for (int lt = issuer; lt < ntaps; lt += HALO_ISSUERS) {
                 const int tap = tap0 + lt;
                 const int r = tap / 3, s = tap - r * 3;
@@ -619,11 +638,18 @@ extern "C" int pdnn_conv_halo_wgrad_bf16(const void* x, const void* dy, int batc
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
     const int combos = p.n_cin_blocks * p.n_cout_blocks;
     if (grid < 2 * combos) grid = 2 * combos;
-    // taps 0..5 carry twice the MMA work of taps 6..8 but the same TMA traffic: 3 : 2 split of the CTAs, in whole combos
-    int a = grid * 3 / 5 / combos * combos;
+    // filter rows 0..1 carry twice the MMA work of row 2 but the same TMA traffic. Measured (ResNet-18 b1024 step): 2 : 1
+    // split of the CTAs 6.98 ms, 3 : 2 7.02 ms, 72 % 7.07 ms with the N = 192 form; the N = 64 form preferred 3 : 2.
+    static const bool narrow = getenv("PDNN_HALO_WGRAD_N64") != nullptr;
+    int a = (narrow ? grid * 3 / 5 : grid * 2 / 3) / combos * combos;
     if (a < combos) a = combos;
     if (grid - a < combos) a = grid - combos;
     p.ctas_group_a = a;
+    p.wide = narrow ? 0 : 1;
+    if (const char* e = getenv("PDNN_HALO_WGRAD_SPLIT")) {      // percentage of the CTAs on filter rows 0..1 (tuning knob)
+        int a2 = grid * atoi(e) / 100 / combos * combos;
+        if (a2 >= combos && grid - a2 >= combos) p.ctas_group_a = a2;
+    }
     conv_halo_wgrad_kernel<<<grid, HALO_THREADS, smem, stream>>>(tmDY, tmX, p);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
