@@ -207,6 +207,32 @@ def gemm_cluster():
 
 
 @case
+def flip_multi():
+    """Mirrored filter banks of several convs in one launch (tiled transpose and the element-wise fallback)."""
+    F = _F()
+    ok = True
+    shapes = [(64, 3, 3, 64), (128, 3, 3, 64), (128, 1, 1, 64), (512, 3, 3, 256), (48, 3, 3, 40)]
+    total = sum(k * r * s * c for (k, r, s, c) in shapes)
+    flat = torch.randn(total + 64, device="cuda").bfloat16()
+    rows, outs, off = [], [], 16
+    for (k, r, s, c) in shapes:
+        o = torch.zeros(c, r, s, k, device="cuda", dtype=torch.bfloat16)
+        outs.append(o)
+        rows.append([off, o.data_ptr(), k, r, s, c])
+        off += k * r * s * c
+    table = torch.tensor(rows, dtype=torch.long).cuda()
+    F.wgt_flip_transpose_multi(flat, table, len(shapes))
+    off = 16
+    for (k, r, s, c), o in zip(shapes, outs):
+        w = flat[off: off + k * r * s * c].view(k, r, s, c)
+        ref = F.wgt_flip_transpose(w)
+        tref = w.flip(1, 2).permute(3, 1, 2, 0).contiguous()
+        ok &= report(f"flip_multi[{k}x{r}x{s}x{c}]", max(rel_err(o, ref), rel_err(o, tref)), 1e-6)
+        off += k * r * s * c
+    return ok
+
+
+@case
 def conv_stem():
     """Stem conv (C <= 3 -> 64): output, the im2col by-product and the BatchNorm statistics."""
     F = _F()

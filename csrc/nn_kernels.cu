@@ -97,12 +97,41 @@ __global__ void wgt_flip_transpose_kernel(const __nv_bfloat16* __restrict__ w, _
 
 // All convolutions of a network in one launch: blockIdx.y picks the layer from a device table of
 // {source offset in the flat weight buffer, destination address, K, R, S, C} (six 64-bit words per layer).
-__global__ void wgt_flip_transpose_multi_kernel(const __nv_bfloat16* __restrict__ w_flat, const long long* __restrict__ table) {
+// wt[c][R-1-r][S-1-s][k] = w[k][r][s][c] is a (k, c) transpose per filter tap: 32x32 tiles go through shared memory so
+// that both the read (along c) and the write (along k) are coalesced (the element-wise form read one 2-byte value per
+// 128-byte line and took 244 us for ResNet-18's 11 M parameters; this one is bound by 45 MB of traffic).
+__global__ void __launch_bounds__(256) wgt_flip_transpose_multi_kernel(const __nv_bfloat16* __restrict__ w_flat, const long long* __restrict__ table) {
+    __shared__ __nv_bfloat16 tile[32][34];
     const long long* e = table + 6 * blockIdx.y;
     const __nv_bfloat16* w = w_flat + e[0];
     __nv_bfloat16* wt = reinterpret_cast<__nv_bfloat16*>(e[1]);
     const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
-    const long long total = (long long)K * R * S * C;
+    const int RS = R * S;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8
+    if ((K & 31) == 0 && (C & 31) == 0) {
+        const int kt = K / 32, ct = C / 32;
+        const int tiles = RS * kt * ct;
+        for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+            const int c0 = (t % ct) * 32;
+            const int k0 = ((t / ct) % kt) * 32;
+            const int rs = t / (ct * kt);
+            const int rs_m = RS - 1 - rs;                         // (R-1-r) * S + (S-1-s)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int kk = ty + j * 8;
+                tile[kk][tx] = w[((long long)(k0 + kk) * RS + rs) * C + c0 + tx];
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int cc = ty + j * 8;
+                wt[((long long)(c0 + cc) * RS + rs_m) * K + k0 + tx] = tile[tx][cc];
+            }
+            __syncthreads();
+        }
+        return;
+    }
+    const long long total = (long long)K * RS * C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int k = (int)(i % K);
         const int s2 = (int)((i / K) % S);

@@ -180,7 +180,7 @@ def conv_wgrad(x, dy, *, R, S, pad, out=None, k_splits=0):
     return out
 
 
-def wgt_flip_transpose_multi(w_flat, table, n_layers, blocks_per_layer=32):
+def wgt_flip_transpose_multi(w_flat, table, n_layers, blocks_per_layer=64):
     """One launch for all mirrored filter banks of a network (see pdnn_wgt_flip_transpose_multi for the table)."""
     call("pdnn_wgt_flip_transpose_multi", w_flat, table, n_layers, blocks_per_layer, stream_ptr())
 
