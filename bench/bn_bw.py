@@ -30,7 +30,7 @@ def main():
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     tot = {}
-    for (m, c) in [(1024 * 32 * 32, 64), (1024 * 16 * 16, 128), (1024 * 8 * 8, 256), (1024 * 4 * 4, 512)]:
+    for (m, c) in [(1024 * 32 * 32, 256), (1024 * 32 * 32, 64), (1024 * 16 * 16, 128), (1024 * 8 * 8, 256), (1024 * 4 * 4, 512)]:
         x = torch.randn(m, c, device="cuda").bfloat16()
         dy = torch.randn(m, c, device="cuda").bfloat16()
         y = torch.empty_like(x); dx = torch.empty_like(x); dres = torch.empty_like(x)
