@@ -87,3 +87,14 @@ def test_evaluator_rank_and_interval_policy(tmp_path):
     assert all(r["selected"] == [0] for r in log[1:])
     rows = open(os.path.join(str(tmp_path), "time_loss_out_SyncReplicas")).read().strip().splitlines()
     assert len(rows) == 3 and all(len(r.split()) == 4 for r in rows)
+
+
+def test_backup_dist_example_two_ranks_stay_in_sync():
+    """pytorch_code/backup/dist_nn_test.py counterpart on gloo: all-reduce-averaged replicas end bit-equal (asserted
+    inside the script) and rank 0 logs the loss."""
+    from pytorch_distributed_nn_b200.parallel.launch import spawn_local
+    outs = spawn_local(["-m", "pytorch_distributed_nn_b200.backup.dist_nn_test", "--steps", "6", "--batch-size", "16"], 2, timeout=180,
+                       env={"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")})
+    for rc, o in outs:
+        assert rc == 0, o[-2000:]
+    assert "Train step 5 world 2" in outs[0][1]

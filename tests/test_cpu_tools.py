@@ -48,3 +48,35 @@ def test_plot_scripts_summarise_reference_file_formats(tmp_path):
     tl.write_text("0.0 1 1\n1.0 1 0\n2.0 1 0\n5.0 2 1\n6.0 2 0\n")
     steps, avg = summarize(str(tl))
     assert abs(avg - 1.5) < 1e-9 and len(steps[1]["arrivals"]) == 2
+
+
+def test_backup_hook_walkthrough_order_and_scaling():
+    """pytorch_code/backup/back_ward_hook_test.py counterpart: the tensor hook fires between the two layers' backward
+    and scales what the lower layer receives by 0.1."""
+    from pytorch_distributed_nn_b200.backup.back_ward_hook_test import run
+    events, ratio = run(log=lambda *_: None)
+    assert events.count("function backward") == 2 and "module hook" in events and "tensor hook" in events
+    assert events.index("tensor hook") < len(events) - 1 and events[0] == "function backward"
+    assert abs(ratio - 0.1) < 1e-5
+
+
+def test_backup_dist_example_single_process_loss_falls():
+    from pytorch_distributed_nn_b200.backup.dist_nn_test import train
+    losses = train(steps=60, batch_size=64, lr=0.05, log=lambda *_: None)
+    assert sum(losses[-10:]) / 10 < sum(losses[:10]) / 10
+
+
+def test_cluster_download_verbs(tmp_path):
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("cluster_tool", os.path.join(os.path.dirname(os.path.dirname(__file__)), "tools", "cluster.py"))
+    ct = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ct)
+    src = tmp_path / "remote" / "outfiles"
+    src.mkdir(parents=True)
+    (src / "time_loss_out_x").write_text("1 2 3 4\n")
+    cfg = ct.Cfg({"hosts": ["127.0.0.1"], "repo_dir": str(tmp_path), "ssh_user": "nobody"})
+    got = ct.download(cfg, str(src), str(tmp_path / "local"), recursive=True)
+    assert len(got) == 1 and os.path.exists(os.path.join(got[0], "time_loss_out_x"))
+    got = ct.download(cfg, str(src / "time_loss_out_x"), str(tmp_path / "local2"), recursive=False)
+    assert len(got) == 1 and open(got[0]).read() == "1 2 3 4\n"

@@ -11,6 +11,8 @@ by ssh), so the same verbs act on a *host list* instead of an AWS account:
     python tools/cluster.py kill_all_python --cfg ...                       # kills only the PIDs this tool started
     python tools/cluster.py list_running --cfg ...
     python tools/cluster.py shutdown   --cfg ...                            # kill + remove the state file
+    python tools/cluster.py download_file   --cfg ... <remote path> <local dir>   # one file from every host
+    python tools/cluster.py download_outdir --cfg ... <remote dir>  <local dir>   # a log / checkpoint directory
 
 The config is a python-literal dict with ``%(key)s`` self-interpolation, like the reference's ``Cfg``
 (tools/pytorch_ec2.py:12-20). Nothing is ever killed by pattern: PIDs (process groups) are recorded in a state file.
@@ -142,6 +144,38 @@ def run_command(cfg, command):
             subprocess.call(f"ssh -o StrictHostKeyChecking=no {cfg['ssh_user']}@{host} {shlex.quote(command)}", shell=True)
 
 
+def download(cfg, remote, local_dir, recursive):
+    """Collect a file / directory from every host into local_dir/<host>/ (reference: tf_ec2.py download_file /
+    download_outdir through the vendored scp module; here the system scp, or a plain copy for local hosts)."""
+    import shutil
+    done = []
+    for host in cfg["hosts"]:
+        dst = os.path.join(local_dir, host.replace(":", "_"))
+        os.makedirs(dst, exist_ok=True)
+        if is_local(host):
+            src = remote if os.path.isabs(remote) else os.path.join(cfg["repo_dir"], remote)
+            if not os.path.exists(src):
+                print(f"{host}: {src} does not exist")
+                continue
+            target = os.path.join(dst, os.path.basename(src.rstrip("/")))
+            if os.path.isdir(src):
+                if not recursive:
+                    print(f"{host}: {src} is a directory (use download_outdir)")
+                    continue
+                shutil.copytree(src, target, dirs_exist_ok=True)
+            else:
+                shutil.copy2(src, target)
+            done.append(target)
+        else:
+            flag = "-r " if recursive else ""
+            rc = subprocess.call(f"scp -o StrictHostKeyChecking=no {flag}{cfg['ssh_user']}@{host}:{shlex.quote(remote)} {shlex.quote(dst)}/", shell=True)
+            if rc == 0:
+                done.append(os.path.join(dst, os.path.basename(remote.rstrip("/"))))
+    for d in done:
+        print("downloaded", d)
+    return done
+
+
 def wait(cfg, timeout):
     t0 = time.time()
     while time.time() - t0 < timeout:
@@ -161,7 +195,8 @@ def wait(cfg, timeout):
 
 def main(argv=None):
     ap = argparse.ArgumentParser()
-    ap.add_argument("command", choices=["launch", "get_hosts", "shutdown", "kill_all_python", "kill_python", "run_command", "list_running", "wait"])
+    ap.add_argument("command", choices=["launch", "get_hosts", "shutdown", "kill_all_python", "kill_python", "run_command", "list_running", "wait",
+                                        "download_file", "download_outdir"])
     ap.add_argument("--cfg", default=os.path.join(ROOT, "configs", "cluster_local.cfg"))
     ap.add_argument("--timeout", type=float, default=600)
     ap.add_argument("rest", nargs=argparse.REMAINDER)
@@ -185,6 +220,10 @@ def main(argv=None):
         list_running(cfg)
     elif a.command == "wait":
         sys.exit(0 if wait(cfg, a.timeout) else 1)
+    elif a.command in ("download_file", "download_outdir"):
+        if len(rest) != 2:
+            ap.error(f"{a.command} <remote path> <local dir>")
+        download(cfg, rest[0], rest[1], recursive=(a.command == "download_outdir"))
 
 
 if __name__ == "__main__":
