@@ -180,30 +180,40 @@ def conv_halo_diag():
     return ok
 
 
-@case
-def gemm_cluster():
-    """The two-CTA cluster schedule (TMA multicast of B, multicast stage release) against the fp32 reference."""
+def _cluster_cases(mode, tag):
     from pytorch_distributed_nn_b200.ops import _lib
     F = _F()
     ok = True
     lib = _lib.lib()
-    prev = lib.pdnn_set_cluster_mode(1)
+    prev = lib.pdnn_set_cluster_mode(mode)
     try:
-        for (M, N, K) in [(512, 256, 512), (1024, 128, 192), (4096, 512, 1024), (37 * 256, 384, 320)]:
+        for (M, N, K) in [(1024, 128, 192), (37 * 256, 384, 320), (512, 256, 512), (4096, 512, 1024)]:
             a = torch.randn(M, K, device="cuda").bfloat16()
             b = torch.randn(N, K, device="cuda").bfloat16()
             res = torch.randn(M, N, device="cuda").bfloat16()
             out = F.gemm(a, b, residual=res, relu=True)
             ref = torch.relu(a.float() @ b.float().t() + res.float())
-            ok &= report(f"gemm_cluster[{M}x{N}x{K}]", rel_err(out, ref), 1.5e-2)
+            ok &= report(f"gemm_{tag}[{M}x{N}x{K}]", rel_err(out, ref), 1.5e-2)
         for (n, h, c, k) in [(8, 16, 128, 128), (64, 8, 256, 256), (304, 4, 512, 512)]:
             x = torch.randn(n, h, h, c, device="cuda").bfloat16()
             w = (torch.randn(k, 3, 3, c, device="cuda") / (3 * c ** 0.5)).bfloat16()
             out = F.conv_fprop(x, w, pad=1)
-            ok &= report(f"conv_cluster[n{n} {h}x{h} c{c} k{k}]", rel_err(out, _conv_ref(x, w, 1)), 1.5e-2)
+            ok &= report(f"conv_{tag}[n{n} {h}x{h} c{c} k{k}]", rel_err(out, _conv_ref(x, w, 1)), 1.5e-2)
     finally:
         lib.pdnn_set_cluster_mode(prev)
     return ok
+
+
+@case
+def gemm_cluster():
+    """The two-CTA cluster schedule (TMA multicast of B, multicast stage release) against the fp32 reference."""
+    return _cluster_cases(1, "cluster")
+
+
+@case
+def gemm_pair():
+    """The CTA-pair schedule (cta_group::2, M = 256 MMAs over both CTAs' shared memory) against the fp32 reference."""
+    return _cluster_cases(2, "pair")
 
 
 @case

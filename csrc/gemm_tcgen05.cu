@@ -72,6 +72,10 @@ struct SmemLayout {
 // CL == 2: launched as clusters of two CTAs that work on two M-tiles of the same N-tile at the same time; each CTA fetches
 // half of every B (filter / weight) tile and TMA-multicasts it into both, so the L2 -> SMEM traffic for B is halved
 // (these kernels are bound by that feed, not by the tensor pipe). K-major B only, no split-K.
+// CL == 3: the same pairing as a CTA PAIR (cta_group::2). Each CTA loads its own A tile and only ITS half of the B tile;
+// the leader (cluster rank 0) issues M = 256 MMAs that read both CTAs' shared memory and write each CTA's own TMEM. Every
+// SM then ingests 16 KB + B/2 per k-block instead of 16 KB + B: ncu shows these kernels bound by that ingest (tensor pipe
+// 51 % active on the stage-3 conv), which multicast cannot change because it still delivers all of B to every SM.
 template <int AMODE, int BMODE, int BN, int CL = 1>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -80,12 +84,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int STAGES = L::STAGES;
     constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
+    constexpr bool CLUSTER = (CL >= 2);       // two CTAs per cluster, tiles (t, t + 1) = two M-tiles of one N-tile
+    constexpr bool PAIR = (CL == 3);          // cta_group::2
     uint32_t cta_rank = 0;
-    if (CL == 2) cta_rank = cluster_ctarank();
+    if (CLUSTER) cta_rank = cluster_ctarank();
     if (p.guard_closed != nullptr) {
         // one thread samples the guard so that the whole CTA (the whole cluster) takes the same branch
         __shared__ uint32_t s_abort;
-        if (CL == 2) {
+        if (CLUSTER) {
             if (threadIdx.x == 0 && cta_rank == 0) {
                 const uint32_t v = ld_relaxed_sys(p.guard_closed) >= ld_relaxed_sys(p.guard_step) ? 1u : 0u;
                 s_abort = v;
@@ -109,6 +115,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    auto peer_full_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 5 + s); };   // PAIR, leader: the peer's stage s landed
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -120,21 +127,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), CL);      // in a cluster a stage is free once BOTH CTAs consumed it
+            mbar_init(empty_bar(s), CL == 2 ? 2 : 1);   // multicast pair: a stage is free once BOTH CTAs consumed it
+            if (PAIR) mbar_init(peer_full_bar(s), 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull_bar(a), 1);
-            mbar_init(tempty_bar(a), 4);
+            mbar_init(tempty_bar(a), PAIR ? 8 : 4);     // pair: the leader's barrier collects both CTAs' epilogue warps
         }
         mbar_fence_init();
     }
     if (warp == 2) {
-        tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
-        tmem_relinquish();
+        if (PAIR) {
+            tmem_alloc_2cta(smem_u32(tmem_slot), TMEM_COLS);
+            tmem_relinquish_2cta();
+        } else {
+            tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
     __syncthreads();
-    if (CL == 2) cluster_sync_all();          // the peer's barriers exist before anything is sent to them
+    if (CLUSTER) cluster_sync_all();          // the peer's barriers exist before anything is sent to them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -150,8 +163,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int ks = tile % p.k_splits;
                 const int rest = tile / p.k_splits;
                 // cluster: M-tile fastest, so that the two CTAs of a cluster (tiles t, t + 1) share the N-tile
-                const int nt = (CL == 2) ? rest / p.m_tiles : rest % p.n_tiles;
-                const int mt = (CL == 2) ? rest % p.m_tiles : rest / p.n_tiles;
+                const int nt = CLUSTER ? rest / p.m_tiles : rest % p.n_tiles;
+                const int mt = CLUSTER ? rest % p.m_tiles : rest / p.n_tiles;
                 const int k_begin = ks * p.k_iters_per_split;
                 const int k_end = min(k_begin + p.k_iters_per_split, p.k_iters_total);
                 // per-tile constants of the conv modes
@@ -173,7 +186,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
                     const uint32_t sb = sa + L::A_BYTES;
                     const uint32_t fb = full_bar(stage);
-                    mbar_expect_tx(fb, L::STAGE_BYTES);
+                    mbar_expect_tx(fb, PAIR ? (uint32_t)(L::A_BYTES + L::B_BYTES / 2) : (uint32_t)L::STAGE_BYTES);
                     // ---- A ----
                     if (AMODE == OP_K2D) {
                         tma_load_2d(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
@@ -198,7 +211,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             const int t = kit / p.cblks;
                             kcol = p.tap_koff[t] + (kit - t * p.cblks) * BLOCK_K;
                         }
-                        if (CL == 2)     // my half of the rows, into both CTAs
+                        if (PAIR)        // my half of the rows, into my own stage (the pair MMA reads both halves in place)
+                            tma_load_2d(sb, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2));
+                        else if (CL == 2)     // my half of the rows, into both CTAs
                             tma_load_2d_multicast(sb + cta_rank * (BN / 2) * 128, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2),
                                                   (uint16_t)0x3);
                         else
@@ -233,20 +248,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ===================== MMA issuer =====================
         constexpr uint32_t A_MN = (AMODE == OP_MN2D) ? 1u : 0u;
         constexpr uint32_t B_MN = (BMODE == OP_MN2D || BMODE == OP_CONVMN || BMODE == OP_CONVMN_G3) ? 1u : 0u;
-        constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, A_MN, B_MN);
+        constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BLOCK_M : BLOCK_M, BN, A_MN, B_MN);
         int stage = 0;
         uint32_t phase = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
+        if (PAIR && cta_rank != 0) {
+            // The peer issues no MMA. It relays "my stage s has landed" to the leader, whose MMAs read this CTA's shared
+            // memory in place. It cannot run ahead: its producer refills a stage only after the leader's commit freed it.
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                for (int kit = 0; kit < p.k_iters_total; ++kit) {
+                    mbar_wait(full_bar(stage), phase);
+                    if (lane == 0) mbar_arrive_remote(peer_full_bar(stage), 0u);
+                    __syncwarp();
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        } else
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int ks = tile % p.k_splits;
             const int k_begin = ks * p.k_iters_per_split;
             const int k_end = min(k_begin + p.k_iters_per_split, p.k_iters_total);
-            mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+            if (PAIR) mbar_wait_cluster(tempty_bar(acc), acc_phase ^ 1);
+            else mbar_wait(tempty_bar(acc), acc_phase ^ 1);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * BN;
             for (int kit = k_begin; kit < k_end; ++kit) {
                 mbar_wait(full_bar(stage), phase);
+                if (PAIR) mbar_wait_cluster(peer_full_bar(stage), phase);
                 tc_fence_after();
                 {
                     const uint32_t issue = lane == 0 ? 1u : 0u;
@@ -262,11 +291,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         const uint64_t adesc = a0 + (uint64_t)(k * (A_MN ? 128 : 2));
                         const uint64_t bdesc = b0 + (uint64_t)(k * (B_MN ? 128 : 2));
-                        umma_bf16_ss_pred(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u, issue);
+                        if (PAIR) umma_bf16_ss_pred_2cta(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u, issue);
+                        else umma_bf16_ss_pred(tmem_d, adesc, bdesc, idesc, (kit > k_begin || k > 0) ? 1u : 0u, issue);
                     }
-                    if (CL == 2) umma_commit_multicast_pred(empty_bar(stage), (uint16_t)0x3, issue);
-                    else umma_commit_pred(empty_bar(stage), issue);
-                    if (kit == k_end - 1) umma_commit_pred(tfull_bar(acc), issue);
+                    if (PAIR) {          // both CTAs' stages / accumulators are released or published by the one commit
+                        umma_commit_2cta_multicast_pred(empty_bar(stage), (uint16_t)0x3, issue);
+                        if (kit == k_end - 1) umma_commit_2cta_multicast_pred(tfull_bar(acc), (uint16_t)0x3, issue);
+                    } else {
+                        if (CL == 2) umma_commit_multicast_pred(empty_bar(stage), (uint16_t)0x3, issue);
+                        else umma_commit_pred(empty_bar(stage), issue);
+                        if (kit == k_end - 1) umma_commit_pred(tfull_bar(acc), issue);
+                    }
                 }
                 __syncwarp();
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -280,8 +315,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int rest = tile / p.k_splits;
-            const int nt = (CL == 2) ? rest / p.m_tiles : rest % p.n_tiles;
-            const int mt = (CL == 2) ? rest % p.m_tiles : rest / p.n_tiles;
+            const int nt = CLUSTER ? rest / p.m_tiles : rest % p.n_tiles;
+            const int mt = CLUSTER ? rest % p.m_tiles : rest / p.n_tiles;
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             long long row = (long long)mt * BLOCK_M + ew * 32 + lane;
@@ -419,17 +454,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (lane == 0) {
+                if (PAIR && cta_rank != 0) mbar_arrive_remote(tempty_bar(acc), 0u);     // the leader's barrier counts all eight warps
+                else mbar_arrive(tempty_bar(acc));
+            }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (CL == 2) cluster_sync_all();          // nobody leaves while the peer can still write into it or signal it
+    if (CLUSTER) cluster_sync_all();          // nobody leaves while the peer can still write into it or signal it
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        if (PAIR) tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+        else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -512,11 +551,11 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 
 // Cluster-of-two launch (see the kernel comment). The grid is two CTAs per cluster that can be co-resident, so that
 // the persistent loop still runs as one wave.
-template <int AMODE, int BMODE, int BN>
+template <int AMODE, int BMODE, int BN, int CLV>
 static int launch_gemm_cluster(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
                                cudaStream_t stream) {
     using L = SmemLayout<BN>;
-    auto kern = gemm_tcgen05_kernel<AMODE, BMODE, BN, 2>;
+    auto kern = gemm_tcgen05_kernel<AMODE, BMODE, BN, CLV>;
     static int max_clusters = -1;
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute at[1];
@@ -547,10 +586,24 @@ static int launch_gemm_cluster(const CUtensorMap& tmA, const CUtensorMap& tmB, c
 // Opt-in (PDNN_CLUSTER=1): measured on B200 the multicast schedule is numerically identical and exactly as fast as
 // the single-CTA one (conv 3x3 n1024 8x8 c256 k256: 72.6 us vs 72.3 us; 16x16 c128 k128: 120.4 vs 118.4 us) -- these
 // shapes are bound by the tensor pipe / wave quantisation (512 tiles on 148 CTAs), not by the B feed from L2.
-static int g_cluster_mode = -1;   // -1: not read yet
-static bool want_cluster(int bn, const GemmParams& p) {
-    if (g_cluster_mode < 0) g_cluster_mode = (getenv("PDNN_CLUSTER") != nullptr && getenv("PDNN_CLUSTER")[0] == '1') ? 1 : 0;
-    return g_cluster_mode == 1 && bn >= 128 && p.k_splits == 1 && (p.m_tiles % 2) == 0 && p.m_tiles * p.n_tiles >= 4 && p.out_remap == 0;
+static int g_cluster_mode = -1;   // -1: not read yet; 0 off, 1 multicast pair (CL = 2), 2 CTA pair / cta_group::2 (CL = 3)
+static int want_cluster(int bn, const GemmParams& p) {
+    if (g_cluster_mode < 0) {
+        const char* e = getenv("PDNN_CLUSTER");
+        g_cluster_mode = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+    }
+    const bool ok = bn >= 128 && p.k_splits == 1 && (p.m_tiles % 2) == 0 && p.m_tiles * p.n_tiles >= 4 && p.out_remap == 0;
+    return ok ? g_cluster_mode : 0;
+}
+template <int AMODE, int BMODE>
+static int dispatch_cluster(int mode, int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
+                            cudaStream_t stream) {
+    if (mode == 2) {
+        if (bn == 128) return launch_gemm_cluster<AMODE, BMODE, 128, 3>(tmA, tmB, p, max_ctas, stream);
+        return launch_gemm_cluster<AMODE, BMODE, 256, 3>(tmA, tmB, p, max_ctas, stream);
+    }
+    if (bn == 128) return launch_gemm_cluster<AMODE, BMODE, 128, 2>(tmA, tmB, p, max_ctas, stream);
+    return launch_gemm_cluster<AMODE, BMODE, 256, 2>(tmA, tmB, p, max_ctas, stream);
 }
 
 template <int AMODE, int BMODE>
@@ -604,7 +657,7 @@ using namespace pdnn;
 
 extern "C" int pdnn_set_cluster_mode(int on) {
     const int prev = pdnn::g_cluster_mode;
-    pdnn::g_cluster_mode = on ? 1 : 0;
+    pdnn::g_cluster_mode = (on == 1 || on == 2) ? on : 0;
     return prev < 0 ? 0 : prev;
 }
 
@@ -643,7 +696,7 @@ extern "C" int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, cons
     p.k_splits = (p.out_mode == 2) ? choose_splits(p.m_tiles * p.n_tiles, p.k_iters_total, k_splits) : 1;
     finish_splits(p);
     p.H = p.W = 1;
-    const bool cluster = !a_mn_major && !b_mn_major && want_cluster(bn, p);
+    const int cluster = (!a_mn_major && !b_mn_major) ? want_cluster(bn, p) : 0;
     {
         long long dims[2], str[2];
         int box[2];
@@ -652,10 +705,7 @@ extern "C" int pdnn_gemm_bf16(const void* A, int a_mn_major, long long lda, cons
         else             { dims[0] = N; dims[1] = K; str[1] = ldb; box[0] = 64; box[1] = 64; }
         if (int rc = make_tmap_bf16(&tmB, B, 2, dims, str, box)) return rc;
     }
-    if (cluster) {
-        if (bn == 128) return launch_gemm_cluster<OP_K2D, OP_K2D, 128>(tmA, tmB, p, epi->max_ctas, stream);
-        return launch_gemm_cluster<OP_K2D, OP_K2D, 256>(tmA, tmB, p, epi->max_ctas, stream);
-    }
+    if (cluster) return dispatch_cluster<OP_K2D, OP_K2D>(cluster, bn, tmA, tmB, p, epi->max_ctas, stream);
     if (!a_mn_major && !b_mn_major) return dispatch_bn<OP_K2D, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
     if (!a_mn_major && b_mn_major) return dispatch_bn<OP_K2D, OP_MN2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
     if (a_mn_major && b_mn_major) return dispatch_bn<OP_MN2D, OP_MN2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
@@ -709,17 +759,14 @@ extern "C" int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, i
     p.H = H; p.W = W; p.C = C; p.R = R; p.S = S; p.pad = pad;
     p.cblks = C / 64;
     fill_epilogue(p, epi);
-    const bool cluster = want_cluster(bn, p);
+    const int cluster = want_cluster(bn, p);
     {
         long long wd[2] = {(long long)R * S * C, Kout};
         long long ws[2] = {1, (long long)R * S * C};
         int wb[2] = {64, cluster ? bn / 2 : bn};
         if (int rc = make_tmap_bf16(&tmB, wgt, 2, wd, ws, wb)) return rc;
     }
-    if (cluster) {
-        if (bn == 128) return launch_gemm_cluster<OP_CONVK, OP_K2D, 128>(tmA, tmB, p, epi->max_ctas, stream);
-        return launch_gemm_cluster<OP_CONVK, OP_K2D, 256>(tmA, tmB, p, epi->max_ctas, stream);
-    }
+    if (cluster) return dispatch_cluster<OP_CONVK, OP_K2D>(cluster, bn, tmA, tmB, p, epi->max_ctas, stream);
     return dispatch_bn<OP_CONVK, OP_K2D>(bn, tmA, tmB, p, epi->max_ctas, stream);
 }
 
