@@ -233,6 +233,27 @@ __device__ __forceinline__ void umma_commit_2cta_multicast_pred(uint32_t bar, ui
         ::"r"(bar), "h"(cta_mask), "r"(issue)
         : "memory");
 }
+// TMA loads of a CTA pair: the data lands in THIS CTA's shared memory, the complete_tx goes to the mbarrier at the same
+// offset in the pair's leader (cluster rank 0), whose one barrier then covers both CTAs' halves of a stage.
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t local_saddr, uint32_t cta_rank) {
+    uint32_t ra;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_saddr), "r"(cta_rank));
+    return ra;
+}
+__device__ __forceinline__ void tma_load_2d_2cta(uint32_t dst, const void* tmap, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(tmap), "r"(leader_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_2cta(uint32_t dst, const void* tmap, uint32_t leader_bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(tmap), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 // arrive on the mbarrier at the same offset in another CTA of the cluster (release at cluster scope)
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t local_bar, uint32_t cta_rank) {
     asm volatile(

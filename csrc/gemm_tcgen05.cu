@@ -115,7 +115,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-    auto peer_full_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 5 + s); };   // PAIR, leader: the peer's stage s landed
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -128,7 +127,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full_bar(s), 1);
             mbar_init(empty_bar(s), CL == 2 ? 2 : 1);   // multicast pair: a stage is free once BOTH CTAs consumed it
-            if (PAIR) mbar_init(peer_full_bar(s), 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull_bar(a), 1);
@@ -185,11 +183,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     mbar_wait(empty_bar(stage), phase ^ 1);
                     const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
                     const uint32_t sb = sa + L::A_BYTES;
-                    const uint32_t fb = full_bar(stage);
-                    mbar_expect_tx(fb, PAIR ? (uint32_t)(L::A_BYTES + L::B_BYTES / 2) : (uint32_t)L::STAGE_BYTES);
+                    // pair: ONE barrier (the leader's) collects the bytes of both CTAs' halves of the stage; the peer's loads
+                    // land in the peer's shared memory and signal that barrier (cta_group::2 form of the TMA load)
+                    const bool peer = PAIR && cta_rank != 0;
+                    const uint32_t fb = peer ? mapa_rank(full_bar(stage), 0u) : full_bar(stage);
+                    if (!peer) mbar_expect_tx(fb, PAIR ? (uint32_t)(2 * (L::A_BYTES + L::B_BYTES / 2)) : (uint32_t)L::STAGE_BYTES);
                     // ---- A ----
                     if (AMODE == OP_K2D) {
-                        tma_load_2d(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
+                        if (peer) tma_load_2d_2cta(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
+                        else tma_load_2d(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
                     } else if (AMODE == OP_MN2D) {
                         tma_load_2d(sa, &tmA, fb, mt * BLOCK_M, kit * BLOCK_K);
                         tma_load_2d(sa + 8192, &tmA, fb, mt * BLOCK_M + 64, kit * BLOCK_K);
@@ -201,7 +203,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         } else {
                             const int r = rs / p.S;
                             const int s = rs - r * p.S;
-                            tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
+                            if (peer) tma_load_4d_2cta(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
+                            else tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
                         }
                     }
                     // ---- B ----
@@ -211,8 +214,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             const int t = kit / p.cblks;
                             kcol = p.tap_koff[t] + (kit - t * p.cblks) * BLOCK_K;
                         }
-                        if (PAIR)        // my half of the rows, into my own stage (the pair MMA reads both halves in place)
-                            tma_load_2d(sb, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2));
+                        if (peer)        // my half of the rows, into my own stage (the pair MMA reads both halves in place)
+                            tma_load_2d_2cta(sb, &tmB, fb, kcol, nt * BN + (BN / 2));
+                        else if (PAIR)
+                            tma_load_2d(sb, &tmB, fb, kcol, nt * BN);
                         else if (CL == 2)     // my half of the rows, into both CTAs
                             tma_load_2d_multicast(sb + cta_rank * (BN / 2) * 128, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2),
                                                   (uint16_t)0x3);
@@ -254,16 +259,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int acc = 0;
         uint32_t acc_phase = 0;
         if (PAIR && cta_rank != 0) {
-            // The peer issues no MMA. It relays "my stage s has landed" to the leader, whose MMAs read this CTA's shared
-            // memory in place. It cannot run ahead: its producer refills a stage only after the leader's commit freed it.
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                for (int kit = 0; kit < p.k_iters_total; ++kit) {
-                    mbar_wait(full_bar(stage), phase);
-                    if (lane == 0) mbar_arrive_remote(peer_full_bar(stage), 0u);
-                    __syncwarp();
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
-                }
-            }
+            // the peer issues no MMA: the leader's M = 256 instructions read this CTA's shared memory and write its TMEM
         } else
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int ks = tile % p.k_splits;
@@ -274,8 +270,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * BN;
             for (int kit = k_begin; kit < k_end; ++kit) {
-                mbar_wait(full_bar(stage), phase);
-                if (PAIR) mbar_wait_cluster(peer_full_bar(stage), phase);
+                if (PAIR) mbar_wait_cluster(full_bar(stage), phase);     // completed by both CTAs' loads
+                else mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
                 {
                     const uint32_t issue = lane == 0 ? 1u : 0u;
