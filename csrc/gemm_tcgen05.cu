@@ -59,12 +59,14 @@ struct GemmParams {
     const uint32_t* guard_step;
 };
 
-template <int BN>
+// HALF_B: CTA-pair mode, a stage holds the A tile and only this CTA's half of the B tile -> more stages fit
+template <int BN, bool HALF_B = false>
 struct SmemLayout {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KiB
-    static constexpr int B_BYTES = BN * BLOCK_K * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN <= 64) ? 8 : (BN <= 128 ? 6 : 4);
+    static constexpr int B_BYTES = BN * BLOCK_K * 2;        // the whole N tile (the pair MMA sees it as two halves)
+    static constexpr int B_LOCAL = HALF_B ? B_BYTES / 2 : B_BYTES;
+    static constexpr int STAGE_BYTES = A_BYTES + B_LOCAL;
+    static constexpr int STAGES = HALF_B ? (BN <= 128 ? 8 : 6) : ((BN <= 64) ? 8 : (BN <= 128 ? 6 : 4));
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
     static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
 };
@@ -80,7 +82,7 @@ template <int AMODE, int BMODE, int BN, int CL = 1>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmParams p) {
-    using L = SmemLayout<BN>;
+    using L = SmemLayout<BN, CL == 3>;
     constexpr int STAGES = L::STAGES;
     constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
@@ -187,7 +189,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     // land in the peer's shared memory and signal that barrier (cta_group::2 form of the TMA load)
                     const bool peer = PAIR && cta_rank != 0;
                     const uint32_t fb = peer ? mapa_rank(full_bar(stage), 0u) : full_bar(stage);
-                    if (!peer) mbar_expect_tx(fb, PAIR ? (uint32_t)(2 * (L::A_BYTES + L::B_BYTES / 2)) : (uint32_t)L::STAGE_BYTES);
+                    if (!peer) mbar_expect_tx(fb, PAIR ? (uint32_t)(2 * L::STAGE_BYTES) : (uint32_t)L::STAGE_BYTES);
                     // ---- A ----
                     if (AMODE == OP_K2D) {
                         if (peer) tma_load_2d_2cta(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
@@ -550,7 +552,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 template <int AMODE, int BMODE, int BN, int CLV>
 static int launch_gemm_cluster(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
                                cudaStream_t stream) {
-    using L = SmemLayout<BN>;
+    using L = SmemLayout<BN, CLV == 3>;
     auto kern = gemm_tcgen05_kernel<AMODE, BMODE, BN, CLV>;
     static int max_clusters = -1;
     cudaLaunchConfig_t cfg{};
