@@ -513,6 +513,12 @@ def elementwise():
     ok &= report("col_sum", rel_err(F.col_sum(d[:, :10], Ccols=10, ld=24), d[:, :10].float().sum(0)), 1e-3)
     f = torch.randn(3, 7, 28, 28, device="cuda")
     ok &= report("nchw_to_nhwc", rel_err(F.nchw_to_nhwc(f, c_pad=8)[..., :7], f.permute(0, 2, 3, 1)), 1e-2)
+    f3 = torch.randn(5, 3, 32, 32, device="cuda")          # image staging path: one thread per pixel
+    ok &= report("nchw_to_nhwc_rgb", rel_err(F.nchw_to_nhwc(f3), f3.permute(0, 2, 3, 1)), 1e-2)
+    x12 = torch.randn(3, 4, 4, 12, device="cuda").bfloat16()   # C % 8 != 0: scalar pooling kernels
+    ok &= report("avgpool_c12", rel_err(F.avgpool(x12), x12.float().mean(dim=(1, 2))), 1e-2)
+    d12 = torch.randn(3, 12, device="cuda").bfloat16()
+    ok &= report("avgpool_bwd_c12", rel_err(F.avgpool_backward(d12, 16), (d12.float() / 16)[:, None, :].expand(3, 16, 12)), 1e-2)
     w = torch.randn(16, 5, 3, 3, device="cuda")
     k = F.oihw_to_krsc(w)
     ok &= report("oihw_to_krsc", rel_err(k, w.permute(0, 2, 3, 1)), 0)

@@ -101,6 +101,20 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__
     }
 }
 
+// image staging (C <= 4, no padding): one thread per pixel -> every channel plane is read with full 128-byte warps and the
+// pixel's channels leave as one contiguous group
+template <typename T>
+__global__ void nchw_to_nhwc_pixel_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C, long long HW) {
+    const long long total = (long long)N * HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long n = i / HW;
+        const long long p = i - n * HW;
+        const float* src = x + n * C * HW + p;
+        T* dst = y + i * C;
+        for (int c = 0; c < C; ++c) dst[c] = from_f<T>(__ldg(src + (long long)c * HW));
+    }
+}
+
 // wt[c][R-1-r][S-1-s][k] = w[k][r][s][c]
 __global__ void wgt_flip_transpose_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt, int K, int R, int S, int C) {
     const long long total = (long long)K * R * S * C;
@@ -623,6 +637,38 @@ __global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
         y[i] = __float2bfloat16(acc * inv);
     }
 }
+// 8 channels per thread (C % 8 == 0): 16-byte accesses, one scale per vector instead of one division chain per element
+__global__ void avgpool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C8) {
+    const long long total = (long long)N * C8;
+    const float inv = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % C8);
+        const long long n = i / C8;
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int p = 0; p < HW; ++p) {
+            float v[8];
+            load8(x + ((n * HW + p) * C8 + c8) * 8, v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += v[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] *= inv;
+        store8(y + i * 8, acc);
+    }
+}
+__global__ void avgpool_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C8) {
+    const long long total = (long long)N * HW * C8;
+    const float inv = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % C8);
+        const long long n = i / ((long long)HW * C8);
+        float v[8];
+        load8(dy + (n * C8 + c8) * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= inv;
+        store8(dx + i * 8, v);
+    }
+}
 __global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
     const long long total = (long long)N * HW * C;
     const float inv = 1.f / (float)HW;
@@ -849,7 +895,10 @@ extern "C" int pdnn_cast_bf16_to_f32(const void* src, float* dst, long long n, v
     LAUNCH_OK();
 }
 extern "C" int pdnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, void* stream) {
-    nchw_to_nhwc_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * Cpad, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, H, W, Cpad);
+    if (C <= 4 && Cpad == C)
+        nchw_to_nhwc_pixel_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, (long long)H * W);
+    else
+        nchw_to_nhwc_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * Cpad, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, H, W, Cpad);
     LAUNCH_OK();
 }
 extern "C" int pdnn_nchw_f32_to_nhwc_f32(const float* x, float* y, int N, int C, int H, int W, int Cpad, void* stream) {
@@ -1004,11 +1053,13 @@ extern "C" int pdnn_maxpool2_bwd_f32(const float* x, const float* y, const float
     LAUNCH_OK();
 }
 extern "C" int pdnn_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
-    avgpool_fwd_kernel<<<grid_for((long long)N * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C);
+    if (C % 8 == 0) avgpool_fwd_vec8_kernel<<<grid_for((long long)N * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C / 8);
+    else avgpool_fwd_kernel<<<grid_for((long long)N * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C);
     LAUNCH_OK();
 }
 extern "C" int pdnn_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
-    avgpool_bwd_kernel<<<grid_for((long long)N * HW * C, 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C);
+    if (C % 8 == 0) avgpool_bwd_vec8_kernel<<<grid_for((long long)N * HW * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C / 8);
+    else avgpool_bwd_kernel<<<grid_for((long long)N * HW * C, 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C);
     LAUNCH_OK();
 }
 extern "C" int pdnn_col_sum(const void* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream) {
