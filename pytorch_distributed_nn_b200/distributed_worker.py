@@ -18,7 +18,7 @@ import torch.nn as nn
 
 from .nn_ops import NN_Trainer
 from .parallel.comm import TERMINATE_STEP
-from .parallel.protocol import STEP_START_, TAG_GRAD_BASE, TAG_WEIGHT_BASE
+from .parallel.protocol import STEP_START_, TAG_WEIGHT_BASE
 from .utils.metrics import JsonlLogger
 
 __all__ = ["ModelBuffer", "DistributedWorker"]

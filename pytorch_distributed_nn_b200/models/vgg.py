@@ -1,7 +1,6 @@
 """CIFAR VGG-11/13/16/19 with BatchNorm (north-star addition: the reference snapshot ships no VGG).
 3x3 convs (with bias) + BN + ReLU, 2x2 max pools, one linear classifier on the 512-d 1x1 feature map."""
 import torch.nn as nn
-import torch.nn.functional as F
 
 from .split import SplitNet, Step
 

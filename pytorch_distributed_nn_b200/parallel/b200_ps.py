@@ -29,7 +29,7 @@ import torch
 from ..engine.network import Network, build_network
 from ..ops import _lib
 from ..ops import functional as F
-from .peer import PeerArena, make_arena
+from .peer import make_arena
 from .protocol import AVG_MODES, STEP_START_
 
 U32 = 4

@@ -16,13 +16,12 @@ The reference hands an ``MPI.COMM_WORLD`` object to its roles and lets models ca
 from __future__ import annotations
 
 import os
-import time
-from typing import Dict, List, Optional
+from typing import List, Optional
 
 import torch
 import torch.distributed as dist
 
-from .protocol import KILL_SIGNAL, TAG_GRAD_BASE, TAG_KILL, TAG_STEP, TAG_WEIGHT_BASE
+from .protocol import KILL_SIGNAL, TAG_GRAD_BASE, TAG_KILL, TAG_STEP
 
 TERMINATE_STEP = -1
 

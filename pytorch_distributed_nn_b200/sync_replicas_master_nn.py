@@ -19,13 +19,13 @@ from __future__ import annotations
 
 import queue
 import time
-from typing import List, Optional
+from typing import List
 
 import torch
 
 from .nn_ops import NN_Trainer
 from .parallel.comm import TERMINATE_STEP, TorchDistCommunicator
-from .parallel.protocol import MAX_NUM_ITERATIONS, STEP_START_, TAG_GRAD_BASE, TAG_WEIGHT_BASE
+from .parallel.protocol import MAX_NUM_ITERATIONS, STEP_START_, TAG_WEIGHT_BASE
 from .utils import checkpoint as ckpt
 from .utils.metrics import JsonlLogger, StepTimer, Timeline
 
