@@ -19,7 +19,6 @@ from __future__ import annotations
 
 from typing import Callable, List, Optional, Sequence
 
-import torch
 import torch.nn as nn
 
 GRAD_TAG_BASE = 88   # reference: tag = 88 + parameter index (sync_replicas_master_nn.py:278-281)
