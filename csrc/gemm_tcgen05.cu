@@ -185,14 +185,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     mbar_wait(empty_bar(stage), phase ^ 1);
                     const uint32_t sa = smem_base + stage * L::STAGE_BYTES;
                     const uint32_t sb = sa + L::A_BYTES;
-                    // pair: ONE barrier (the leader's) collects the bytes of both CTAs' halves of the stage; the peer's loads
-                    // land in the peer's shared memory and signal that barrier (cta_group::2 form of the TMA load)
-                    const bool peer = PAIR && cta_rank != 0;
-                    const uint32_t fb = peer ? mapa_rank(full_bar(stage), 0u) : full_bar(stage);
-                    if (!peer) mbar_expect_tx(fb, PAIR ? (uint32_t)(2 * L::STAGE_BYTES) : (uint32_t)L::STAGE_BYTES);
+                    // pair: ONE barrier (the leader's) collects the bytes of both CTAs' halves of the stage; every load lands in
+                    // the issuing CTA's shared memory and signals that barrier (cta_group::2 form of the TMA load)
+                    // (both CTAs use the cta_group::2 form: with the leader on the plain form the convs ran 12 % slower)
+                    const bool pair_ld = PAIR;
+                    const uint32_t fb = PAIR ? mapa_rank(full_bar(stage), 0u) : full_bar(stage);
+                    if (!PAIR || cta_rank == 0) mbar_expect_tx(full_bar(stage), PAIR ? (uint32_t)(2 * L::STAGE_BYTES) : (uint32_t)L::STAGE_BYTES);
                     // ---- A ----
                     if (AMODE == OP_K2D) {
-                        if (peer) tma_load_2d_2cta(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
+                        if (pair_ld) tma_load_2d_2cta(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
                         else tma_load_2d(sa, &tmA, fb, kit * BLOCK_K, mt * BLOCK_M);
                     } else if (AMODE == OP_MN2D) {
                         tma_load_2d(sa, &tmA, fb, mt * BLOCK_M, kit * BLOCK_K);
@@ -205,7 +206,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         } else {
                             const int r = rs / p.S;
                             const int s = rs - r * p.S;
-                            if (peer) tma_load_4d_2cta(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
+                            if (pair_ld) tma_load_4d_2cta(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
                             else tma_load_4d(sa, &tmA, fb, cb * BLOCK_K, s - p.pad, a_h0 * p.stride + r - p.pad, a_n0);
                         }
                     }
@@ -216,10 +217,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             const int t = kit / p.cblks;
                             kcol = p.tap_koff[t] + (kit - t * p.cblks) * BLOCK_K;
                         }
-                        if (peer)        // my half of the rows, into my own stage (the pair MMA reads both halves in place)
-                            tma_load_2d_2cta(sb, &tmB, fb, kcol, nt * BN + (BN / 2));
-                        else if (PAIR)
-                            tma_load_2d(sb, &tmB, fb, kcol, nt * BN);
+                        if (pair_ld)     // my half of the rows, into my own stage (the pair MMA reads both halves in place)
+                            tma_load_2d_2cta(sb, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2));
                         else if (CL == 2)     // my half of the rows, into both CTAs
                             tma_load_2d_multicast(sb + cta_rank * (BN / 2) * 128, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2),
                                                   (uint16_t)0x3);
