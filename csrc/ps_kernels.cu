@@ -168,6 +168,16 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
                                  : "l"(reinterpret_cast<const float*>(a.multicast_slots) + i * 4)
                                  : "memory");
                 }
+                if (a.poison_slots) {      // one multicast store poisons this element in every worker's local slot
+                    if (a.slot_is_bf16)
+                        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(
+                                         const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots)) + i * 4),
+                                     "r"(0x7FC07FC0u), "r"(0x7FC07FC0u) : "memory");
+                    else
+                        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(
+                                         const_cast<float*>(reinterpret_cast<const float*>(a.multicast_slots)) + i * 4),
+                                     "r"(0x7FC00000u), "r"(0x7FC00000u), "r"(0x7FC00000u), "r"(0x7FC00000u) : "memory");
+                }
             } else
             for (int w = 0; w < a.n_workers; ++w) {
                 if (!(mask & (1u << w))) continue;
@@ -175,9 +185,15 @@ __global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_consta
                     const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w]) + i * 4);
                     const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
                     acc.x += lo.x; acc.y += lo.y; acc.z += hi.x; acc.w += hi.y;
+                    if (a.poison_slots)
+                        *reinterpret_cast<uint2*>(const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w])) + i * 4) =
+                            make_uint2(0x7FC07FC0u, 0x7FC07FC0u);
                 } else {
                     const float4 g = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.slots[w]) + i * 4);
                     acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+                    if (a.poison_slots)
+                        *reinterpret_cast<uint4*>(const_cast<float*>(reinterpret_cast<const float*>(a.slots[w])) + i * 4) =
+                            make_uint4(0x7FC00000u, 0x7FC00000u, 0x7FC00000u, 0x7FC00000u);
                 }
             }
             float4 m = reinterpret_cast<float4*>(a.momentum)[i];

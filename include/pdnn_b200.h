@@ -235,6 +235,10 @@ typedef struct pdnn_ps_master {
     int max_ctas;
     uint32_t* step_ptr;                      /* non-NULL: read `step` from this device word and advance it at the end, so
                                                 that the launch does not depend on the step number (CUDA-graph replay) */
+    int poison_slots;                        /* debug (race detection): overwrite every gradient slot the master has summed
+                                                with NaN, inside the same kernel and before the workers are released. A
+                                                slot that is ever summed without having been rewritten for its step then
+                                                turns the weights into NaN instead of silently reusing stale data. */
 } pdnn_ps_master_t;
 
 /* Master: wait for the first k arrivals of `step`, publish the kill mask to the late workers

@@ -39,6 +39,7 @@ class PSMaster(C.Structure):
         ("n", C.c_longlong), ("n_workers", C.c_int), ("k", C.c_int), ("slot_is_bf16", C.c_int),
         ("weights_are_bf16", C.c_int), ("avg_mode", C.c_int), ("lr", C.c_float), ("mu", C.c_float),
         ("step", C.c_uint32), ("deadline_ns", C.c_longlong), ("max_ctas", C.c_int), ("step_ptr", C.c_void_p),
+        ("poison_slots", C.c_int),
     ]
 
 

@@ -45,8 +45,11 @@ class B200ParameterServer:
                  momentum: float = 0.0, num_aggregate: Optional[int] = None, avg_mode: str = "k",
                  grad_dtype: str = "bf16", colocate: bool = True, n_buckets: int = 8, seed: int = 0,
                  deadline_ms: float = 0.0, delay_fn: Optional[Callable[[int, int], int]] = None, group=None,
-                 device=None, init_state_dict=None):
+                 device=None, init_state_dict=None, poison_slots: Optional[bool] = None):
         assert torch.cuda.is_available(), "the b200 backend needs a GPU (use --backend gloo on CPU)"
+        # race-detection mode: the master kernel overwrites every slot it has summed with NaN before releasing
+        # the workers; a gradient that is ever consumed twice (stale step) shows up as NaN weights. Env: PDNN_PS_POISON=1.
+        self.poison_slots = (os.environ.get("PDNN_PS_POISON") == "1") if poison_slots is None else bool(poison_slots)
         self.rank, self.world = rank, world_size
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.colocate = colocate or world_size == 1
@@ -161,6 +164,7 @@ class B200ParameterServer:
             m.lr, m.mu = self.lr, self.mu
             m.deadline_ns = self.deadline_ns
             m.max_ctas = 0
+            m.poison_slots = int(self.poison_slots)
             self._margs = m
             self.result = self.flags[M_RESULT: M_RESULT + 8]
             self.history = []
@@ -248,6 +252,12 @@ class B200ParameterServer:
             self._graph_loss = self._step_body(self._gx, self._gy)
         self.graph_kernel_launches = _lib.launch_count() - n0      # library kernels inside one replay
         return self
+
+    def local_slot(self, w: int) -> torch.Tensor:
+        """Rank 0, unicast-slot mode: the master-side gradient slot of worker ``w`` as a tensor (tests, debugging)."""
+        assert self.is_master and not self.nvls_gather, "slots live on the workers in NVLS gather mode"
+        dt = torch.bfloat16 if self.grad_bf16 else torch.float32
+        return self.arena.tensor(self.off_slots[w], self.net.total * self.slot_elem, dt)
 
     def _step_body(self, x, y):
         loss = None

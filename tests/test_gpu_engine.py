@@ -230,3 +230,24 @@ def test_cuda_graph_replay_matches_eager_steps():
     assert b.last_result() == (1, 0, 1, 5) and float(loss) == float(loss)
     assert torch.allclose(b.net.w32, wa, rtol=1e-4, atol=1e-5)
     b.close()
+
+
+def test_poisoned_slots_leave_training_unchanged_and_end_up_nan():
+    """Race-detection mode of the master kernel: every summed slot is overwritten with NaN before the workers are
+    released. Training must not notice (each step's gradients are rewritten before they are summed), and the slot must be
+    all-NaN after a step."""
+    from pytorch_distributed_nn_b200.parallel.b200_ps import B200ParameterServer
+    x = [torch.randn(32, 1, 28, 28, device="cuda") for _ in range(3)]
+    y = [torch.randint(0, 10, (32,), device="cuda") for _ in range(3)]
+    out = []
+    for poison in (False, True):
+        ps = B200ParameterServer("LeNet", 32, 0, 1, lr=0.05, momentum=0.5, seed=3, grad_dtype="fp32", poison_slots=poison)
+        for i in range(3):
+            ps.train_step(x[i], y[i])
+        torch.cuda.synchronize()
+        assert ps.last_result()[3] == 3
+        if poison:
+            assert bool(torch.isnan(ps.local_slot(0)[: ps.net.total]).all())
+        out.append(ps.net.w32.clone())
+        ps.close()
+    assert bool(torch.isfinite(out[1]).all()) and torch.allclose(out[0], out[1], rtol=1e-4, atol=1e-5)
