@@ -54,14 +54,10 @@ Bottleneck = R.Bottleneck
 class ResNetSplit(SplitNet):
     def __init__(self, block, num_blocks, num_classes=10):
         super().__init__()
-        self.in_planes = 64
-        self.conv1 = nn.Conv2d(3, 64, 3, 1, 1, bias=False)
-        self.bn1 = nn.BatchNorm2d(64)
-        self.layer1 = self._stage(block, 64, num_blocks[0], 1)
-        self.layer2 = self._stage(block, 128, num_blocks[1], 2)
-        self.layer3 = self._stage(block, 256, num_blocks[2], 2)
-        self.layer4 = self._stage(block, 512, num_blocks[3], 2)
-        self.linear = nn.Linear(512 * block.expansion, num_classes)
+        self.conv1 = nn.Conv2d(3, R.STAGE_WIDTHS[0], 3, 1, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(R.STAGE_WIDTHS[0])
+        width = R.build_stages(self, block, num_blocks)
+        self.linear = nn.Linear(width, num_classes)
         steps = [
             Step("conv1", self.conv1, ["x"], "stem.c", [self.conv1]),
             Step("bn1", self.bn1, ["stem.c"], "stem.b", [self.bn1]),
@@ -78,8 +74,6 @@ class ResNetSplit(SplitNet):
             Step("linear", self.linear, ["pooled"], "out", [self.linear]),
         ]
         self.set_steps(steps)
-
-    _stage = R.ResNet._stage
 
     def name(self):
         return "resnet"
