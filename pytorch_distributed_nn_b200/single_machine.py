@@ -37,7 +37,7 @@ def main(argv=None):
     hist = trainer.train(_Loader(train_set, args.batch_size))
     if args.train_dir:
         from .utils.checkpoint import save_checkpoint
-        save_checkpoint(args.train_dir, len(hist), trainer.state_dict())
+        save_checkpoint(args.train_dir, hist[-1]["step"] if hist else 0, trainer.state_dict())   # named after the last step taken
     return hist
 
 

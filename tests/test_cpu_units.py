@@ -213,3 +213,47 @@ def test_ddp_comparator_single_process_is_identity():
     out.sum().backward()
     net.finish_backward()
     assert len(net.buckets) >= 1 and all(p.grad is not None for p in net.module.parameters())
+
+
+def test_cifar10_pickle_reader_keeps_channel_planes(tmp_path):
+    """The python pickles store each image as 3 planes of 1024 bytes (CHW). The reference reshapes an NHWC array to NCHW
+    without transposing (cifar10/cifar10.py:67-70); here plane c of image i must come back as [i, c]."""
+    import pickle
+    import numpy as np
+    from pytorch_distributed_nn_b200.utils.data import read_cifar10
+    root = tmp_path / "cifar-10-batches-py"
+    root.mkdir()
+    rng = np.random.RandomState(0)
+
+    def dump(name, n, base):
+        data = rng.randint(0, 256, size=(n, 3072)).astype(np.uint8)
+        data[:, :1024] = base          # red plane constant: easy to recognise after loading
+        with open(root / name, "wb") as f:
+            pickle.dump({"data": data, "labels": [int(i % 10) for i in range(n)]}, f)
+        return data
+    for i in range(1, 6):
+        dump(f"data_batch_{i}", 4, 10 * i)
+    test = dump("test_batch", 3, 77)
+    ds = read_cifar10(str(tmp_path))
+    assert ds.train.images.shape == (20, 3, 32, 32) and ds.validation.images.shape == (3, 3, 32, 32)
+    assert float(ds.validation.images[:, 0].min()) == 77.0 and float(ds.validation.images[:, 0].max()) == 77.0
+    # the reader shuffles: every loaded image must be one of the pickled rows, plane for plane
+    for img in ds.validation.images:
+        assert any((img.reshape(-1) == row.astype(np.float32)).all() for row in test)
+    nhwc = read_cifar10(str(tmp_path), reshape=False)
+    assert nhwc.validation.images.shape == (3, 32, 32, 3) and float(nhwc.validation.images[..., 0].max()) == 77.0
+    padded = read_cifar10(str(tmp_path), padding_size=2)
+    assert padded.train.images.shape == (20, 3, 36, 36) and float(padded.train.images[:, :, 0, :].max()) == 0.0
+
+
+def test_single_machine_cpu_trains_lenet_and_writes_a_state_dict(tmp_path):
+    """pytorch_code/single_machine.py counterpart on the CPU path (torch modules + optim.SGD, nn_ops/__init__.py:46-85)."""
+    from pytorch_distributed_nn_b200 import single_machine
+    from pytorch_distributed_nn_b200.utils.checkpoint import latest_checkpoint, load_checkpoint
+    hist = single_machine.main(["--network", "LeNet", "--dataset", "MNIST", "--synthetic", "--no-cuda", "--batch-size", "32",
+                                "--max-steps", "30", "--lr", "0.05", "--log-interval", "1", "--train-dir", str(tmp_path)])
+    assert [h["step"] for h in hist] == list(range(1, 31))
+    assert all(h["loss"] == h["loss"] and h["loss"] < 10 for h in hist)            # finite, sane
+    path, step = latest_checkpoint(str(tmp_path))
+    sd = load_checkpoint(path)[0]
+    assert step == 30 and "conv1.weight" in sd and sd["fc2.bias"].shape == (10,)
