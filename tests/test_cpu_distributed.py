@@ -98,3 +98,16 @@ def test_backup_dist_example_two_ranks_stay_in_sync():
     for rc, o in outs:
         assert rc == 0, o[-2000:]
     assert "Train step 5 world 2" in outs[0][1]
+
+
+def test_comm_test_two_ranks_deliver_all_eight_lenet_gradients():
+    """pytorch_code/comm_test/comm_test.py counterpart: rank 1 streams the eight LeNet parameter gradients (float64 wire),
+    rank 0 receives every one of them with its shape."""
+    from pytorch_distributed_nn_b200.parallel.launch import spawn_local
+    outs = spawn_local(["-m", "pytorch_distributed_nn_b200.comm_test"], 2, timeout=180,
+                       env={"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")})
+    for rc, o in outs:
+        assert rc == 0, o[-2000:]
+    got = [l for l in outs[0][1].splitlines() if l.startswith("master received grad of tensor")]
+    assert len(got) == 8
+    assert any("shape (500, 800)" in l for l in got) and any("shape (20, 1, 5, 5)" in l for l in got)
