@@ -257,3 +257,26 @@ def test_single_machine_cpu_trains_lenet_and_writes_a_state_dict(tmp_path):
     path, step = latest_checkpoint(str(tmp_path))
     sd = load_checkpoint(path)[0]
     assert step == 30 and "conv1.weight" in sd and sd["fc2.bias"].shape == (10,)
+
+
+def test_polling_evaluator_restores_the_newest_checkpoint(tmp_path, capsys):
+    """distributed_TF/src/nn_eval.py counterpart: the stand-alone evaluator restores whatever checkpoint is newest in the
+    directory and prints `Num examples ... Precision @ 1 ... Loss ...` (nn_eval.py:49-111)."""
+    import torch
+    from pytorch_distributed_nn_b200.evaluator import evaluate_checkpoints
+    from pytorch_distributed_nn_b200.models import build_model
+    from pytorch_distributed_nn_b200.utils.checkpoint import save_checkpoint
+    from pytorch_distributed_nn_b200.utils.data import read_mnist
+    torch.manual_seed(0)
+    net = build_model("LeNet")
+    save_checkpoint(str(tmp_path), 10, net.state_dict())
+    with torch.no_grad():
+        for p in net.parameters():
+            p.mul_(0.5)
+    save_checkpoint(str(tmp_path), 20, net.state_dict())
+    data = read_mnist(synthetic=True).validation
+    res = evaluate_checkpoints(str(tmp_path), "LeNet", data, run_once=True)
+    assert len(res) == 1 and res[0][0] == 20 and 0.0 <= res[0][2] <= 1.0 and res[0][1] == res[0][1]
+    assert "Precision @ 1" in capsys.readouterr().out
+    # nothing new: a second poll evaluates nothing
+    assert evaluate_checkpoints(str(tmp_path), "LeNet", data, eval_interval_secs=0.01, max_polls=2)[0][0] == 20
