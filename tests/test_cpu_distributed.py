@@ -111,3 +111,37 @@ def test_comm_test_two_ranks_deliver_all_eight_lenet_gradients():
     got = [l for l in outs[0][1].splitlines() if l.startswith("master received grad of tensor")]
     assert len(got) == 8
     assert any("shape (500, 800)" in l for l in got) and any("shape (20, 1, 5, 5)" in l for l in got)
+
+
+_DDP_SNIPPET = r"""
+import torch, torch.distributed as dist
+from pytorch_distributed_nn_b200.parallel.launch import init_distributed
+from pytorch_distributed_nn_b200.data_parallel_dist import DistributedDataParallel
+from pytorch_distributed_nn_b200.models import build_model
+rank, world, _ = init_distributed("gloo")
+torch.manual_seed(0)
+net = DistributedDataParallel(build_model("LeNet"))
+g = torch.Generator().manual_seed(100 + rank)
+x = torch.randn(4, 1, 28, 28, generator=g)
+net(x).square().mean().backward()
+local = [p.grad.clone() for p in net.module.parameters()]
+net.finish_backward()
+flat_local = torch.cat([t.flatten() for t in local])
+gathered = [torch.empty_like(flat_local) for _ in range(world)]
+dist.all_gather(gathered, flat_local)
+want = sum(gathered) / world
+got = torch.cat([p.grad.flatten() for p in net.module.parameters()])
+assert torch.allclose(got, want, atol=1e-6), float((got - want).abs().max())
+print("DDP_OK rank", rank, "buckets", len(net.buckets))
+dist.barrier(); dist.destroy_process_group()
+"""
+
+
+def test_ddp_comparator_two_ranks_average_the_bucketed_gradients():
+    """Vendored-DDP counterpart (pytorch_code/data_parallel_dist/data_parallel_dist.py:70-83, 238-264): bucketed all-reduce
+    leaves every replica with the mean of the local gradients."""
+    from pytorch_distributed_nn_b200.parallel.launch import spawn_local
+    outs = spawn_local(["-c", _DDP_SNIPPET], 2, timeout=180, env={"PYTHONPATH": ROOT + os.pathsep + os.environ.get("PYTHONPATH", "")})
+    for rc, o in outs:
+        assert rc == 0, o[-2000:]
+        assert "DDP_OK" in o
