@@ -1,4 +1,7 @@
 // 3x3 stride-1 pad-1 convolution with halo reuse and resident filters (tcgen05 / TMEM / TMA, sm_100a).
+// Reference layers: every `nn.Conv2d(planes, planes, kernel_size=3, stride=1, padding=1, bias=False)` of BasicBlock
+// (pytorch_code/model_ops/resnet.py:19-22, resnet_split.py:28,34) and the 3x3 convs of the VGG configuration; forward,
+// data gradient (same kernel on mirrored filters) and weight gradient (conv_halo_wgrad_kernel below).
 //
 // The generic implicit-GEMM path (gemm_tcgen05.cu, OP_CONVK) fetches one shifted activation box per filter tap, i.e.
 // every input element travels L2 -> shared memory nine times, and re-fetches the filter tile for every output tile.

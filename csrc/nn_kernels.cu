@@ -3,6 +3,17 @@
 // Activations are NHWC; `T` is __nv_bfloat16 on the tensor-core path and float on the small-shape
 // (LeNet / FC-MLP) path. All kernels use 16-byte accesses where the layout allows it and grid-stride
 // loops sized to the 148 SMs.
+//
+// What each family stands in for in the reference (which runs them through torch 0.2 CPU autograd, numpy or BLAS):
+//   BatchNorm fwd/bwd      nn.BatchNorm2d in pytorch_code/model_ops/resnet.py:20,22,27-29 (training statistics, running buffers)
+//   ReLU / max / avg pool  F.relu, F.max_pool2d in model_ops/lenet.py:27-33; F.avg_pool2d(out, 4) in resnet.py:94
+//   softmax cross-entropy  nn.CrossEntropyLoss in nn_ops/__init__.py:43; Softmax + LogDot in MPI_code/src/util/util.h:125-144;
+//                          SoftmaxOutputLayer in pure_py_code/nn/nn_layer.py:128-145
+//   top-k                  accuracy() in nn_ops/__init__.py:13-26
+//   momentum SGD           optim.SGD in nn_ops/__init__.py:42 and update_params_dist_version, sync_replicas_master_nn.py:22-28
+//   sigmoid family         SigmoidLayer in pure_py_code/nn/nn_layer.py:113-125; Sigmoid / SigmoidDeriv in util.h:101-123
+//   SIMT fp32 GEMM         cblas_dgemm wrappers MatrixMultiply / TransA / TransB in util.h:35-81; numpy dot in nn_layer.py:79-100
+//   im2col / col2im        the lowering torch's CPU conv uses internally for lenet.py:17-18 and the ResNet stems / shortcuts
 #include "common.cuh"
 #include "../include/pdnn_b200.h"
 

@@ -3,6 +3,10 @@
 Conventions: activations NHWC bf16 (``[N,H,W,C]`` contiguous), conv weights KRSC (``[Cout,R,S,Cin]``),
 parameters / gradients fp32. Every function launches on the current CUDA stream and returns its output
 tensor(s); ``out=`` lets the engine pass preallocated buffers so a training step allocates nothing.
+
+These are the ops the reference gets from torch.nn.functional / numpy / CBLAS (pytorch_code/model_ops/lenet.py:27-33,
+resnet.py:19-36,94; pure_py_code/nn/nn_layer.py:58-145; MPI_code/src/util/util.h:21-144); the per-op mapping is in the
+header of csrc/nn_kernels.cu and in include/pdnn_b200.h.
 """
 from __future__ import annotations
 
