@@ -80,3 +80,15 @@ def test_cluster_download_verbs(tmp_path):
     assert len(got) == 1 and os.path.exists(os.path.join(got[0], "time_loss_out_x"))
     got = ct.download(cfg, str(src / "time_loss_out_x"), str(tmp_path / "local2"), recursive=False)
     assert len(got) == 1 and open(got[0]).read() == "1 2 3 4\n"
+
+
+def test_roofline_tool_groups_a_launch_list():
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(__file__))
+    spec = importlib.util.spec_from_file_location("roofline_tool", os.path.join(root, "tools", "roofline_from_launches.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    t, w = m.main([os.path.join(root, "profiles", "launches_resnet18_b1024_v10.csv"), "--network", "ResNet18", "--batch", "1024"])
+    assert t["batchnorm"] > 1000 and t["fprop+dgrad"] > t["wgrad"] > 1000        # microseconds
+    assert abs(w["fprop"] / 1e12 - 1.137) < 0.01 and w["params"] > 11_000_000
