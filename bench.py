@@ -93,6 +93,8 @@ class ClockSampler:
 
 
 def reference_unavailable():
+    if int(os.environ.get("RANK", "0")) != 0:      # under torchrun every rank runs this: one line, from rank 0
+        return 0
     print(json.dumps({"impl": "reference", "unavailable":
                       "reference is not pip-installable (no setup.py/pyproject) and needs Python 2 + torch<=0.3 + mpi4py/mpirun + "
                       "tensorflow, none of which exist in this image; see DESIGN.md and baseline/ for the restated baseline"}))
