@@ -92,19 +92,113 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def reference_unavailable():
-    if int(os.environ.get("RANK", "0")) != 0:      # under torchrun every rank runs this: one line, from rank 0
+def _ref_unavailable(why):
+    if int(os.environ.get("RANK", "0")) == 0:      # under torchrun every rank runs this: one line, from rank 0
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def run_reference(args):
+    """``--impl reference``: the UNMODIFIED reference tree (byte-identical copy under baseline/_ref) runs its own
+    ``pytorch_code/distributed_nn.py`` (master = its SyncReplicasMaster_NN, workers = its DistributedWorker on its
+    ResNetSplit18; reference run line pytorch_code/run_pytorch.sh:1) -- none of this repo's models, kernels or engine.
+    Each torchrun rank starts one reference worker on its GPU (MPI rank r+1); rank 0 also starts the reference's
+    master process (MPI rank 0, host memory, as written). ``baseline/run_reference.py`` documents the environment
+    shims (mpi4py over local sockets, import stubs, torch compatibility patches) and how a step is timed."""
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    ref_dir = os.path.join(ROOT, "baseline", "_ref", "pytorch_code")
+    if not os.path.isdir(ref_dir):
+        src = "/root/reference"
+        if os.path.isdir(os.path.join(src, "pytorch_code")) and rank == 0:
+            import shutil
+            shutil.copytree(src, os.path.join(ROOT, "baseline", "_ref"), symlinks=True, dirs_exist_ok=True,
+                            ignore=shutil.ignore_patterns(".git"))
+        if not os.path.isdir(ref_dir) and world == 1:
+            return _ref_unavailable("baseline/_ref (byte-identical copy of the reference tree) is missing and /root/reference is not mounted")
+    if args.network not in ("ResNet18", "ResNet34", "LeNet"):
+        return _ref_unavailable(f"the reference's distributed entry point builds only LeNet / ResNet18 / ResNet34 "
+                                f"(sync_replicas_master_nn.py:103-109), not {args.network}")
+    import torch
+    have_gpu = torch.cuda.is_available()
+    mode = os.environ.get("PDNN_REF_DEVICE", "cuda" if have_gpu else "cpu")
+    autocast = os.environ.get("PDNN_REF_AUTOCAST", "bf16" if mode == "cuda" else "none")
+    device = f"cuda:{local_rank}" if mode == "cuda" else "cpu"
+    tag = f"{os.getppid()}_{os.environ.get('MASTER_PORT', '0')}" if world > 1 else f"{os.getpid()}_solo"
+    rdv = os.path.join(os.environ.get("PDNN_REF_TMP", "/tmp"), f"pdnn_ref_{tag}")
+    data_dir = os.path.join(os.environ.get("PDNN_REF_TMP", "/tmp"), "pdnn_ref_data")
+    os.makedirs(rdv, exist_ok=True)
+    result = os.path.join(rdv, "result.json")
+    launcher = os.path.join(ROOT, "baseline", "run_reference.py")
+    dataset = "MNIST" if args.network == "LeNet" else "Cifar10"
+    k = args.num_aggregate or world
+    ref_argv = [f"--network={args.network}", f"--dataset={dataset}", f"--batch-size={args.batch_size}", "--comm-type=Bcast",
+                f"--num-aggregate={k}", f"--lr={args.lr}", f"--momentum={args.momentum}"]
+    ncpu = os.cpu_count() or 8
+    threads = max(1, ncpu // (world + 1))
+    common = [sys.executable, launcher, "--mpi-size", str(world + 1), "--rdv", rdv, "--data-dir", data_dir,
+              "--bench", f"{args.warmup},{args.steps}", "--result", result, "--threads", str(threads)]
+    procs = []
+    if rank == 0:
+        procs.append(subprocess.Popen(common + ["--mpi-rank", "0", "--device", "cpu", "--log", os.path.join(rdv, "master.log"), "--"] + ref_argv))
+    procs.append(subprocess.Popen(common + ["--mpi-rank", str(rank + 1), "--device", device, "--autocast", autocast,
+                                            "--log", os.path.join(rdv, f"worker{rank + 1}.log"), "--"] + ref_argv))
+    sampler = ClockSampler(local_rank) if (rank == 0 and have_gpu) else None
+    if sampler:
+        sampler.start()
+    rcs = [p.wait() for p in procs]
+    clocks = sampler.stop() if sampler else None
+    if rank != 0:
         return 0
-    print(json.dumps({"impl": "reference", "unavailable":
-                      "reference is not pip-installable (no setup.py/pyproject) and needs Python 2 + torch<=0.3 + mpi4py/mpirun + "
-                      "tensorflow, none of which exist in this image; see DESIGN.md and baseline/ for the restated baseline"}))
+    if not os.path.exists(result):
+        return _ref_unavailable(f"reference run ended without a result (exit codes {rcs}); logs in {rdv}")
+    with open(result) as f:
+        res = json.load(f)
+    if res.get("status") != "bench_done":
+        return _ref_unavailable(f"reference run stopped early: {res.get('status')} after {res.get('stamps')} step announcements; logs in {rdv}")
+    B, K = args.batch_size, args.steps
+    gb = B * world                      # the reference divides by n and waits for every worker when k = n
+    total_s = res["total_s"]
+    st = sorted(res["step_s"])
+    n_param = {"ResNet18": 11173962, "ResNet34": 21282122, "LeNet": 431080}[args.network]
+    chw = (1, 28, 28) if args.network == "LeNet" else (3, 32, 32)
+    batch_bytes = B * chw[0] * chw[1] * chw[2] * 4 + B * 8
+    value = gb * K / total_s
+    out = {
+        "metric": "images/sec (sync-SGD parameter server, whole job) + p50/p99 step ms",
+        "value": round(value, 1), "unit": "images/sec", "n_gpus": world, "steps": K, "warmup": args.warmup,
+        "ms_per_step": round(total_s / K * 1e3, 4), "p50_step_ms": round(st[len(st) // 2] * 1e3, 4),
+        "p99_step_ms": round(st[min(len(st) - 1, int(len(st) * 0.99))] * 1e3, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16 autocast (fp32 parameters, fp64 wire as written)" if autocast == "bf16" else "fp32 (fp64 wire as written)",
+        "data": "synthetic", "impl": "reference",
+        "config": {"model": args.network, "dataset_shape": "CIFAR-10 (3x32x32, 10 classes)" if chw[0] == 3 else "MNIST (1x28x28)",
+                   "global_batch": gb, "per_worker_batch": B, "seq_len": None,
+                   "parallelism": f"reference PS: 1 master process (host) + {world} worker processes, k={k} of n={world}",
+                   "entry_point": "baseline/_ref/pytorch_code/distributed_nn.py (unmodified) " + " ".join(ref_argv),
+                   "device": device if mode == "cpu" else "one B200 per worker (modules placed by torch.set_default_device; see baseline/ref_shims/pdnn_ref_compat.py)",
+                   "transport": "mpi4py-compatible shim over AF_UNIX sockets (baseline/ref_shims/mpi4py)",
+                   "timing": "host clock between the master's step announcements (tag 10); every step ends with a blocking D2H of all gradients, so the GPU is idle at both edges",
+                   "l2_policy": "inputs come from a 50000-image host array, a new batch every step"},
+        # the reference has one path only: every step copies its batch H2D and reads all gradients + loss back
+        "e2e": {"value": round(value, 1), "unit": "images/sec", "ms_per_step": round(total_s / K * 1e3, 4),
+                "h2d_bytes_per_step": (batch_bytes + 4 * n_param) if mode == "cuda" else 0,
+                "d2h_bytes_per_step": (4 * n_param + 4) if mode == "cuda" else 0},
+        "gpu_launches": None,
+        "mpi_bytes": res.get("traffic"),
+        "clocks": clocks,
+    }
+    print(json.dumps(out))
+    import shutil
+    shutil.rmtree(rdv, ignore_errors=True)
     return 0
 
 
 def main():
     args = parse()
     if args.impl == "reference":
-        return reference_unavailable()
+        return run_reference(args)
     import torch
     import torch.distributed as dist
     from pytorch_distributed_nn_b200.ops import _lib
