@@ -177,8 +177,9 @@ struct Net {
         cudaFree(X); cudaFree(Y); cudaFree(loss); cudaFree(wrong);
         if (stream) cudaStreamDestroy(stream);
     }
-    void fill_batch(const Dataset& d, int* cursor) {
+    void fill_batch(const Dataset& d, int* cursor, int* used = nullptr) {
         if (*cursor + p.batch > d.n) *cursor = 0;
+        if (used != nullptr) *used = *cursor;
         FC_CUDA(cudaMemcpyAsync(X, d.images.data() + (size_t)*cursor * d.dim, sizeof(float) * (size_t)p.batch * d.dim, cudaMemcpyHostToDevice, stream));
         FC_CUDA(cudaMemcpyAsync(Y, d.labels.data() + *cursor, sizeof(long long) * p.batch, cudaMemcpyHostToDevice, stream));
         *cursor += p.batch;
@@ -212,7 +213,7 @@ struct Net {
     }
 };
 
-struct Arrival { int worker, layer, step; };
+struct Arrival { int worker, layer, step, batch_start; };
 
 struct Board {
     NNParams p;
@@ -228,6 +229,17 @@ struct Board {
     std::vector<std::vector<float*>> slots;
     std::vector<float*> acc;
     int master_device = 0;
+    // evaluator hand-over: the master copies the newest weights into We whenever the evaluator is idle, so the evaluator
+    // never reads a buffer the master is writing (Wm[par] is rewritten one step later)
+    std::vector<float*> We;
+    std::mutex mu_eval;
+    std::condition_variable cv_eval;
+    int eval_step = 0;            // step whose weights sit in We (0 = none yet, -1 = finished)
+    bool eval_busy = false;       // evaluator still copying We into its own network
+    bool we_writing = false;      // master is filling We
+    // optional acceptance log for replay against an oracle: (step, worker, layer, batch_start) in accumulation order
+    int* accept_log = nullptr;
+    long long accept_cap = 0, accept_n = 0;
     // statistics
     std::vector<double> step_ms;
     long long accepted = 0, dropped_stale = 0, abandoned_steps = 0;
@@ -259,7 +271,8 @@ static void worker_loop(Board* b, int w, int device, const Dataset* data) {
         }
         if (my_step > b->cfg.n_train_iters || my_step < 0) break;
         const int par = my_step & 1;
-        net.fill_batch(*data, &cursor);
+        int batch_start = 0;
+        net.fill_batch(*data, &cursor, &batch_start);
         bool abandoned = false;
         for (int l = 0; l < L && !abandoned; ++l) {
             if (step_changed()) { abandoned = true; break; }
@@ -277,7 +290,7 @@ static void worker_loop(Board* b, int w, int device, const Dataset* data) {
             cudaStreamSynchronize(net.stream);
             {
                 std::lock_guard<std::mutex> lk(b->mu);
-                b->arrivals.push_back({w, l, my_step});
+                b->arrivals.push_back({w, l, my_step, batch_start});
             }
             b->cv_arrival.notify_one();
         }
@@ -301,14 +314,20 @@ static void evaluator_loop(Board* b, int device, const Dataset* data) {
     FILE* f = fopen(path.c_str(), "w");
     while (!failed.load()) {
         {
-            std::unique_lock<std::mutex> lk(b->mu);
-            b->cv_step.wait(lk, [&] { return b->cur_step.load() != my_step || failed.load(); });
-            my_step = b->cur_step.load();
+            std::unique_lock<std::mutex> lk(b->mu_eval);
+            while (!((b->eval_step != my_step && !b->we_writing) || failed.load())) b->cv_eval.wait_for(lk, std::chrono::milliseconds(100));
+            if (failed.load() || b->eval_step < 0) break;
+            my_step = b->eval_step;
+            b->eval_busy = true;
         }
-        if (my_step < 0) break;
-        const int par = my_step & 1;
         for (int l = 0; l < L; ++l)
-            copy_d2d(net.W[l], device, b->Wm[par][l], b->master_device, sizeof(float) * b->p.layer_elems(l), net.stream);
+            copy_d2d(net.W[l], device, b->We[l], b->master_device, sizeof(float) * b->p.layer_elems(l), net.stream);
+        cudaStreamSynchronize(net.stream);
+        {
+            std::lock_guard<std::mutex> lk(b->mu_eval);
+            b->eval_busy = false;            // We may be refreshed from here on
+        }
+        b->cv_eval.notify_all();
         float loss_sum = 0.f; int wrong_sum = 0, seen = 0, cursor = 0;
         for (int it = 0; it < b->cfg.eval_batches && cursor + b->p.batch <= data->n; ++it) {
             net.fill_batch(*data, &cursor);
@@ -329,10 +348,33 @@ static void evaluator_loop(Board* b, int device, const Dataset* data) {
             b->eval_err.push_back(err);
         }
         if (f) { fprintf(f, "%d %.3f %.6f %.6f\n", my_step, now_ms() - t0, loss, err); fflush(f); }   // step time loss err (evaluator_nn.h:58)
-        if (my_step > b->cfg.n_train_iters) break;
+        if (my_step > b->cfg.n_train_iters) break;      // that was the final model
     }
     if (f) fclose(f);
     net.destroy();
+}
+
+// Weights of `step` (in Wm[step & 1]) -> We, when the evaluator is idle (or, with `must`, after waiting for it).
+static void hand_to_evaluator(Board* b, int step, cudaStream_t stream, bool must) {
+    if (!b->cfg.with_evaluator) return;
+    const int L = b->p.n_layers();
+    {
+        std::unique_lock<std::mutex> lk(b->mu_eval);
+        if (must) { while (b->eval_busy && !b->failed.load()) b->cv_eval.wait_for(lk, std::chrono::milliseconds(100)); }
+        else if (b->eval_busy) return;
+        if (b->failed.load()) return;
+        b->we_writing = true;
+    }
+    // the evaluator reads We only while eval_busy is set, and cannot set it while we_writing is
+    for (int l = 0; l < L; ++l)
+        cudaMemcpyAsync(b->We[l], b->Wm[step & 1][l], sizeof(float) * b->p.layer_elems(l), cudaMemcpyDeviceToDevice, stream);
+    cudaStreamSynchronize(stream);
+    {
+        std::lock_guard<std::mutex> lk(b->mu_eval);
+        b->eval_step = step;
+        b->we_writing = false;
+    }
+    b->cv_eval.notify_all();
 }
 
 static void master_loop(Board* b) {
@@ -351,6 +393,7 @@ static void master_loop(Board* b) {
         std::fill(count.begin(), count.end(), 0);
         for (auto& s : seen) std::fill(s.begin(), s.end(), 0);
         for (int l = 0; l < L; ++l) cudaMemsetAsync(b->acc[l], 0, sizeof(float) * b->p.layer_elems(l), stream);
+        hand_to_evaluator(b, step, stream, false);
         {
             std::lock_guard<std::mutex> lk(b->mu);
             b->cur_step.store(step, std::memory_order_release);      // the step message + weights "broadcast" (weights are already in Wm[par])
@@ -372,6 +415,10 @@ static void master_loop(Board* b) {
             }
             if (seen[a.worker][a.layer]) continue;
             seen[a.worker][a.layer] = 1;
+            if (b->accept_log != nullptr && b->accept_n < b->accept_cap) {
+                int* row = b->accept_log + 4 * b->accept_n++;
+                row[0] = step; row[1] = a.worker; row[2] = a.layer; row[3] = a.batch_start;
+            }
             const long long n = b->p.layer_elems(a.layer);
             axpy_kernel<<<(int)std::min<long long>((n + 255) / 256, 592), 256, 0, stream>>>(b->acc[a.layer], b->slots[a.worker][a.layer], 1.f, n);
             count[a.layer]++;
@@ -389,15 +436,26 @@ static void master_loop(Board* b) {
     }
     {
         std::lock_guard<std::mutex> lk(b->mu);
-        b->cur_step.store(b->cfg.n_train_iters + 1, std::memory_order_release);   // the last step message ends workers and evaluator
+        b->cur_step.store(b->cfg.n_train_iters + 1, std::memory_order_release);   // the last step message ends the workers
     }
     b->cv_step.notify_all();
+    // the evaluator always gets the final model (step n_train_iters + 1), then the end marker
+    if (!failed.load()) hand_to_evaluator(b, b->cfg.n_train_iters + 1, stream, true);
+    {
+        std::unique_lock<std::mutex> lk(b->mu_eval);
+        if (!b->cfg.with_evaluator || failed.load()) b->eval_step = -1;
+    }
+    b->cv_eval.notify_all();
     cudaStreamDestroy(stream);
 }
 
 }  // namespace fcps
 
 extern "C" int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* res) {
+    return pdnn_fc_ps_run_ex(cfg, res, nullptr);
+}
+
+extern "C" int pdnn_fc_ps_run_ex(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* res, pdnn_fc_ps_io_t* io) {
     using namespace fcps;
     PDNN_REQUIRE(cfg != nullptr && res != nullptr, "fc_ps: null arguments");
     Board board;
@@ -428,21 +486,39 @@ extern "C" int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_
     b->slots.assign(cfg->n_workers, std::vector<float*>(L, nullptr));
     for (int par = 0; par < 2; ++par) b->Wm[par].assign(L, nullptr);
     b->acc.assign(L, nullptr);
+    b->We.assign(L, nullptr);
+    if (io != nullptr && io->accept_log != nullptr) { b->accept_log = io->accept_log; b->accept_cap = io->accept_log_rows; }
+    long long w_off = 0;
     for (int l = 0; l < L; ++l) {
         const long long n = b->p.layer_elems(l);
         for (int par = 0; par < 2; ++par) PDNN_CUDA_CHECK(cudaMalloc(&b->Wm[par][l], sizeof(float) * n));
         PDNN_CUDA_CHECK(cudaMalloc(&b->acc[l], sizeof(float) * n));
+        PDNN_CUDA_CHECK(cudaMalloc(&b->We[l], sizeof(float) * n));
         for (int w = 0; w < cfg->n_workers; ++w) PDNN_CUDA_CHECK(cudaMalloc(&b->slots[w][l], sizeof(float) * n));
         // W ~ N(0, 0.1^2), bias row = 0 (pure_py_code/nn/nn_layer.py:58-110)
         std::vector<float> h(n, 0.f);
         std::normal_distribution<float> g(0.f, 0.1f);
         for (long long i = 0; i < (long long)b->p.dims[l] * b->p.dims[l + 1]; ++i) h[i] = g(rng);
-        PDNN_CUDA_CHECK(cudaMemcpy(b->Wm[1][l], h.data(), sizeof(float) * n, cudaMemcpyHostToDevice));   // step 1 reads parity 1
+        const float* src = (io != nullptr && io->init_weights != nullptr) ? io->init_weights + w_off : h.data();
+        PDNN_CUDA_CHECK(cudaMemcpy(b->Wm[1][l], src, sizeof(float) * n, cudaMemcpyHostToDevice));   // step 1 reads parity 1
+        w_off += n;
     }
     Dataset train, test;
-    const bool real = load_mnist(cfg->data_dir, &train, cfg->synthetic_examples > 0 ? cfg->synthetic_examples : 4096, b->p.dims[0], b->p.dims.back(), cfg->seed);
-    if (real) { test = train; test.n = std::min(train.n, 2048); }
-    else synthetic(&test, 1024, b->p.dims[0], b->p.dims.back(), cfg->seed + 99);
+    if (io != nullptr && io->train_images != nullptr) {
+        PDNN_REQUIRE(io->train_labels != nullptr && io->n_train > 0, "fc_ps: caller-provided training set needs labels and a size");
+        train.n = io->n_train; train.dim = b->p.dims[0];
+        train.images.assign(io->train_images, io->train_images + (size_t)io->n_train * train.dim);
+        train.labels.assign(io->train_labels, io->train_labels + io->n_train);
+        if (io->test_images != nullptr && io->n_test > 0) {
+            test.n = io->n_test; test.dim = train.dim;
+            test.images.assign(io->test_images, io->test_images + (size_t)io->n_test * test.dim);
+            test.labels.assign(io->test_labels, io->test_labels + io->n_test);
+        } else { test = train; }
+    } else {
+        const bool real = load_mnist(cfg->data_dir, &train, cfg->synthetic_examples > 0 ? cfg->synthetic_examples : 4096, b->p.dims[0], b->p.dims.back(), cfg->seed);
+        if (real) { test = train; test.n = std::min(train.n, 2048); }
+        else synthetic(&test, 1024, b->p.dims[0], b->p.dims.back(), cfg->seed + 99);
+    }
     PDNN_REQUIRE(train.dim == b->p.dims[0], "fc_ps: dataset dimension %d does not match the input layer %d", train.dim, b->p.dims[0]);
     PDNN_REQUIRE(train.n >= b->p.batch, "fc_ps: dataset smaller than one batch");
 
@@ -479,9 +555,21 @@ extern "C" int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_
         }
     }
     cudaSetDevice(0);
+    if (io != nullptr) {
+        io->accept_log_used = b->accept_n;
+        if (io->final_weights != nullptr && !b->failed.load()) {      // weights of step n_train_iters + 1
+            long long off = 0;
+            for (int l = 0; l < L; ++l) {
+                const long long n = b->p.layer_elems(l);
+                PDNN_CUDA_CHECK(cudaMemcpy(io->final_weights + off, b->Wm[(cfg->n_train_iters + 1) & 1][l], sizeof(float) * n, cudaMemcpyDeviceToHost));
+                off += n;
+            }
+        }
+    }
     for (int l = 0; l < L; ++l) {
         for (int par = 0; par < 2; ++par) cudaFree(b->Wm[par][l]);
         cudaFree(b->acc[l]);
+        cudaFree(b->We[l]);
         for (int w = 0; w < cfg->n_workers; ++w) cudaFree(b->slots[w][l]);
     }
     PDNN_REQUIRE(!b->failed.load(), "fc_ps: a role failed (see stderr)");

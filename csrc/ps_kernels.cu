@@ -28,41 +28,47 @@ __global__ void __launch_bounds__(512) ps_push_kernel(const float* __restrict__ 
                                                       uint32_t* local_counter, const uint32_t* guard_closed,
                                                       const uint32_t* guard_step, const uint32_t* step_ptr) {
     if (step_ptr != nullptr) step = ld_relaxed_sys(step_ptr);   // CUDA-graph mode: the step number lives on the device
-    if (guard_closed != nullptr) {   // a killed worker drops its contribution (CTA-uniform decision)
-        __shared__ int s_abort;
-        if (threadIdx.x == 0) s_abort = ld_relaxed_sys(guard_closed) >= ld_relaxed_sys(guard_step);
-        __syncthreads();
-        if (s_abort) return;
-    }
-    const long long n8 = n / 8;
-    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long nth = (long long)gridDim.x * blockDim.x;
-    if (slot_is_bf16) {
-        __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(slot);
-        for (long long i = tid; i < n8; i += nth) {
-            const float4 a = *reinterpret_cast<const float4*>(grad + i * 8);
-            const float4 b = *reinterpret_cast<const float4*>(grad + i * 8 + 4);
-            uint4 u;
-            u.x = pack_bf16x2(a.x, a.y); u.y = pack_bf16x2(a.z, a.w);
-            u.z = pack_bf16x2(b.x, b.y); u.w = pack_bf16x2(b.z, b.w);
-            st_na_v4(d + i * 8, u);
+    __shared__ int s_abort;
+    if (threadIdx.x == 0) s_abort = guard_closed != nullptr && ld_relaxed_sys(guard_closed) >= ld_relaxed_sys(guard_step);
+    __syncthreads();
+    // a killed worker drops its contribution (CTA-uniform decision). The decision can differ between the CTAs of one
+    // grid (the master's `closed` store may land while the grid is running), so an aborting CTA still takes part in the
+    // completion handshake below and only vetoes the flag: the counter always returns to zero.
+    const bool abort = s_abort != 0;
+    if (abort && flag_peer == nullptr) return;
+    if (!abort) {
+        const long long n8 = n / 8;
+        const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        const long long nth = (long long)gridDim.x * blockDim.x;
+        if (slot_is_bf16) {
+            __nv_bfloat16* d = reinterpret_cast<__nv_bfloat16*>(slot);
+            for (long long i = tid; i < n8; i += nth) {
+                const float4 a = *reinterpret_cast<const float4*>(grad + i * 8);
+                const float4 b = *reinterpret_cast<const float4*>(grad + i * 8 + 4);
+                uint4 u;
+                u.x = pack_bf16x2(a.x, a.y); u.y = pack_bf16x2(a.z, a.w);
+                u.z = pack_bf16x2(b.x, b.y); u.w = pack_bf16x2(b.z, b.w);
+                st_na_v4(d + i * 8, u);
+            }
+            if (tid == 0) for (long long j = n8 * 8; j < n; ++j) d[j] = __float2bfloat16(grad[j]);
+        } else {
+            float* d = reinterpret_cast<float*>(slot);
+            for (long long i = tid; i < n8 * 2; i += nth) st_na_v4(d + i * 4, *reinterpret_cast<const uint4*>(grad + i * 4));
+            if (tid == 0) for (long long j = n8 * 8; j < n; ++j) d[j] = grad[j];
         }
-        if (tid == 0) for (long long j = n8 * 8; j < n; ++j) d[j] = __float2bfloat16(grad[j]);
-    } else {
-        float* d = reinterpret_cast<float*>(slot);
-        for (long long i = tid; i < n8 * 2; i += nth) st_na_v4(d + i * 4, *reinterpret_cast<const uint4*>(grad + i * 4));
-        if (tid == 0) for (long long j = n8 * 8; j < n; ++j) d[j] = grad[j];
+        if (flag_peer == nullptr) return;
     }
-    if (flag_peer == nullptr) return;
-    // grid completion -> one release store of the step-tagged arrival flag
+    // grid completion -> one release store of the step-tagged arrival flag (unless any CTA of the grid aborted)
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
+        if (abort) atomicOr(local_counter + 1, 1u);
         const uint32_t done = atom_add_acqrel_gpu(local_counter, 1u) + 1u;
         if (done == gridDim.x) {
+            const uint32_t vetoed = atomicExch(local_counter + 1, 0u);
             st_relaxed_sys(local_counter, 0u);
             __threadfence_system();
-            st_release_sys(flag_peer, step);
+            if (!vetoed) st_release_sys(flag_peer, step);
         }
     }
 }

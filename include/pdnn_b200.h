@@ -330,6 +330,26 @@ typedef struct pdnn_fc_ps_result {
 } pdnn_fc_ps_result_t;
 
 int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* result);
+
+/* Same run with caller-side inputs / outputs (all HOST pointers, any of them may be NULL): the data set, the initial
+ * weights, the final weights and the list of gradients the master accumulated, in accumulation order. Which gradients
+ * win a step is timing dependent (first n_to_collect per layer, sync_replicas_master_nn.h:71-101); with the log a
+ * caller can replay exactly that set through an oracle. Weight layout: layers concatenated, each
+ * [(dims[l] + 1) x dims[l+1]] row-major with the bias as last row. */
+typedef struct pdnn_fc_ps_io {
+    const float* train_images;       /* [n_train][dims[0]] */
+    const long long* train_labels;
+    int n_train;
+    const float* test_images;        /* evaluator set; NULL = the training set */
+    const long long* test_labels;
+    int n_test;
+    const float* init_weights;       /* NULL = N(0, 0.1^2), zero bias */
+    float* final_weights;            /* out */
+    int* accept_log;                 /* out: rows of (step, worker, layer, first row of the worker's batch) */
+    long long accept_log_rows;       /* capacity in rows */
+    long long accept_log_used;       /* out: rows written */
+} pdnn_fc_ps_io_t;
+int pdnn_fc_ps_run_ex(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* result, pdnn_fc_ps_io_t* io);
 int pdnn_fc_ps_selftest(int iters, float* first_loss, float* last_loss);
 
 #ifdef __cplusplus

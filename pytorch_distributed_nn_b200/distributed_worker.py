@@ -71,10 +71,18 @@ class DistributedWorker(NN_Trainer):
             from .parallel.delays import parse_delay_spec
             delay_fn = parse_delay_spec(self.inject_delay) if self.inject_delay else None
             kw = self.kwargs
+            policy = kw.get("straggler_policy", "kofn" if self._kill_aware else "all")
+            n_workers = self.world_size if self.colocate else self.world_size - 1
+            k = kw.get("kill_threshold")
+            if policy == "all" or not k:
+                k = n_workers
+            interval_ms = float(kw.get("interval_ms", 0.0) or 0.0)
             self.ps = B200ParameterServer(self.network_config, self.batch_size, self.rank, self.world_size, lr=self.lr,
-                                          momentum=self.momentum, num_aggregate=kw.get("kill_threshold"), avg_mode=kw.get("avg_mode", "k"),
+                                          momentum=self.momentum, num_aggregate=max(1, min(int(k), n_workers)), avg_mode=kw.get("avg_mode", "k"),
                                           grad_dtype="bf16" if self.grad_dtype == "bf16" else "fp32", colocate=self.colocate,
-                                          n_buckets=self.n_buckets, delay_fn=delay_fn, group=self.comm.group, device=self.comm.device)
+                                          n_buckets=self.n_buckets, seed=int(kw.get("seed", 1) or 1),
+                                          deadline_ms=interval_ms if policy == "interval" else 0.0, delay_fn=delay_fn,
+                                          group=self.comm.group, device=self.comm.device)
             self.network = self.ps.net
             return self
         from .models import build_model

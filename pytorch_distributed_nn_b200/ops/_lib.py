@@ -64,6 +64,16 @@ class FcPsResult(C.Structure):
     ]
 
 
+class FcPsIO(C.Structure):
+    """Mirror of pdnn_fc_ps_io_t (host pointers)."""
+    _fields_ = [
+        ("train_images", C.c_void_p), ("train_labels", C.c_void_p), ("n_train", C.c_int),
+        ("test_images", C.c_void_p), ("test_labels", C.c_void_p), ("n_test", C.c_int),
+        ("init_weights", C.c_void_p), ("final_weights", C.c_void_p),
+        ("accept_log", C.c_void_p), ("accept_log_rows", C.c_longlong), ("accept_log_used", C.c_longlong),
+    ]
+
+
 _P, _I, _L, _F, _U = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_uint32
 
 # name -> argtypes (stream pointer included where the C function takes one)
@@ -135,6 +145,7 @@ _SIGS = {
     "pdnn_enable_peer_access": [_I],
     "pdnn_bn_fwd_noalloc": [_P, _P, _P, _P, _P, _P, _P, _P, _L, _I, _F, _F, _I, _P],
     "pdnn_fc_ps_run": [C.POINTER(FcPsConfig), C.POINTER(FcPsResult)],
+    "pdnn_fc_ps_run_ex": [C.POINTER(FcPsConfig), C.POINTER(FcPsResult), C.POINTER(FcPsIO)],
     "pdnn_fc_ps_selftest": [_I, C.POINTER(C.c_float), C.POINTER(C.c_float)],
 }
 

@@ -45,7 +45,7 @@ class B200ParameterServer:
                  momentum: float = 0.0, num_aggregate: Optional[int] = None, avg_mode: str = "k",
                  grad_dtype: str = "bf16", colocate: bool = True, n_buckets: int = 8, seed: int = 0,
                  deadline_ms: float = 0.0, delay_fn: Optional[Callable[[int, int], int]] = None, group=None,
-                 device=None, init_state_dict=None, poison_slots: Optional[bool] = None):
+                 device=None, init_state_dict=None, init_momentum=None, poison_slots: Optional[bool] = None):
         assert torch.cuda.is_available(), "the b200 backend needs a GPU (use --backend gloo on CPU)"
         # race-detection mode: the master kernel overwrites every slot it has summed with NaN before releasing
         # the workers; a gradient that is ever consumed twice (stale step) shows up as NaN weights. Env: PDNN_PS_POISON=1.
@@ -68,6 +68,7 @@ class B200ParameterServer:
         self.batch_size = batch_size
         self._graph_mode = False
         self._graph = None
+        self._check_agreement(network, group)
 
         # ---- network (every rank builds it: the master needs the layout, workers need the layers)
         self.net: Network = self._build(network, batch_size, n_buckets, group)
@@ -77,8 +78,25 @@ class B200ParameterServer:
             if init_state_dict is not None:    # resume: the checkpoint replaces the random init before the first broadcast
                 net.load_state_dict(init_state_dict)
             self.momentum = torch.zeros(net.total, device=self.device, dtype=torch.float32)
+            if init_momentum is not None:      # resume: the optimizer state continues as well (TF Supervisor restores everything)
+                assert init_momentum.numel() == net.total, "momentum sidecar does not match this network"
+                self.momentum.copy_(init_momentum.to(self.device, torch.float32).view(-1))
         self._install_hooks()
         self._initial_broadcast(group)
+
+    def _check_agreement(self, network, group):
+        """Every rank derives its data path from (k, n, deadline, wire dtype): a worker that believes k = n writes its
+        gradients into its LOCAL slot for the in-switch sum while a master with k < n reads pushed slots nobody fills.
+        Arrival flags would still fire, so nothing hangs and training silently stops learning -- hence a hard check."""
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        mine = (str(network), self.n_workers, self.k, self.deadline_ns, self.grad_bf16, bool(self.colocate), self.avg_mode)
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine, group=group)
+        if any(tuple(o) != mine for o in everyone):
+            raise RuntimeError("B200ParameterServer: ranks disagree on (network, n_workers, k, deadline_ns, grad_bf16, colocate, avg_mode): "
+                               + "; ".join(f"rank {r}: {o}" for r, o in enumerate(everyone)))
 
     # ---- construction ---------------------------------------------------------------------------
     def _build(self, network, batch, n_buckets, group) -> Network:

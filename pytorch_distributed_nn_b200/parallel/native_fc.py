@@ -17,7 +17,13 @@ from ..ops import _lib
 
 def run_native_fc_ps(dims=DIMS_CPP, batch=128, lr=1e-3, n_workers=6, n_to_collect=2, iters=100, shortcircuit=True,
                      timeline=False, evaluator=True, eval_batches=4, delay_workers=(), delay_us_per_layer=0, seed=1,
-                     synthetic_examples=8192, max_devices=0, data_dir="", out_dir="outfiles") -> dict:
+                     synthetic_examples=8192, max_devices=0, data_dir="", out_dir="outfiles", train=None, test=None,
+                     init_weights=None, want_weights=False, want_log=False) -> dict:
+    """``train`` / ``test``: optional ``(images float32 [n, dims[0]], labels int64 [n])`` CPU tensors; ``init_weights``:
+    list of ``[(dims[l] + 1), dims[l+1]]`` float32 CPU tensors (bias = last row). With ``want_weights`` / ``want_log`` the
+    result gains ``final_weights`` (same list form) and ``accept_log`` (rows ``(step, worker, layer, batch_start)`` in
+    the order the master accumulated them), which is what an oracle needs to replay a timing-dependent run."""
+    import torch
     cfg = _lib.FcPsConfig()
     cfg.n_dims = len(dims)
     for i, d in enumerate(dims):
@@ -31,8 +37,76 @@ def run_native_fc_ps(dims=DIMS_CPP, batch=128, lr=1e-3, n_workers=6, n_to_collec
     cfg.seed, cfg.synthetic_examples, cfg.max_devices = seed, synthetic_examples, max_devices
     cfg.data_dir, cfg.out_dir = data_dir.encode(), out_dir.encode()
     res = _lib.FcPsResult()
-    _lib.call("pdnn_fc_ps_run", C.byref(cfg), C.byref(res))
-    return {f: (getattr(res, f).decode() if f == "scheme" else getattr(res, f)) for f, _ in res._fields_}
+    io = _lib.FcPsIO()
+    keep = []
+    sizes = [(dims[l] + 1) * dims[l + 1] for l in range(len(dims) - 1)]
+    if train is not None:
+        x, y = train[0].contiguous().float(), train[1].contiguous().long()
+        keep += [x, y]
+        io.train_images, io.train_labels, io.n_train = x.data_ptr(), y.data_ptr(), x.shape[0]
+    if test is not None:
+        x, y = test[0].contiguous().float(), test[1].contiguous().long()
+        keep += [x, y]
+        io.test_images, io.test_labels, io.n_test = x.data_ptr(), y.data_ptr(), x.shape[0]
+    if init_weights is not None:
+        flat = torch.cat([w.reshape(-1).float() for w in init_weights]).contiguous()
+        assert flat.numel() == sum(sizes)
+        keep.append(flat)
+        io.init_weights = flat.data_ptr()
+    final = log = None
+    if want_weights:
+        final = torch.zeros(sum(sizes), dtype=torch.float32)
+        io.final_weights = final.data_ptr()
+    if want_log:
+        log = torch.zeros((iters * n_workers * (len(dims) - 1), 4), dtype=torch.int32)
+        io.accept_log, io.accept_log_rows = log.data_ptr(), log.shape[0]
+    _lib.call("pdnn_fc_ps_run_ex", C.byref(cfg), C.byref(res), C.byref(io))
+    out = {f: (getattr(res, f).decode() if f == "scheme" else getattr(res, f)) for f, _ in res._fields_}
+    if final is not None:
+        out["final_weights"] = [t.view(dims[l] + 1, dims[l + 1]) for l, t in enumerate(final.split(sizes))]
+    if log is not None:
+        out["accept_log"] = log[: io.accept_log_used].tolist()
+    return out
+
+
+def oracle_replay(dims, batch, lr, init_weights, train, accept_log, iters):
+    """fp32 PyTorch restatement of the native master's update for exactly the gradients it accumulated:
+    per step and layer, W -= lr / count * sum of the accepted workers' gradients, each computed on that worker's
+    batch with the weights of that step (reference sync_replicas_master_nn.h:71-128, nn_layer.h:97-178)."""
+    import torch
+    X, Y = train[0].double(), train[1].long()
+    W = [w.clone().double() for w in init_weights]
+    L = len(dims) - 1
+    by_step = {}
+    for step, w, l, start in accept_log:
+        by_step.setdefault(step, []).append((w, l, start))
+
+    def grads(start):
+        z = X[start: start + batch]
+        acts = [z]
+        for l in range(L):
+            s = torch.cat([acts[-1], torch.ones(batch, 1, dtype=z.dtype)], 1) @ W[l]
+            acts.append(torch.sigmoid(s) if l < L - 1 else s)
+        d = torch.softmax(acts[-1], 1)
+        d[torch.arange(batch), Y[start: start + batch]] -= 1.0
+        d /= batch
+        out = [None] * L
+        for l in range(L - 1, -1, -1):
+            out[l] = torch.cat([acts[l], torch.ones(batch, 1, dtype=z.dtype)], 1).t() @ d
+            if l > 0:
+                d = (d @ W[l][:-1].t()) * acts[l] * (1 - acts[l])
+        return out
+
+    for step in range(1, iters + 1):
+        cache, acc, cnt = {}, [torch.zeros_like(w) for w in W], [0] * L
+        for w, l, start in by_step.get(step, []):
+            if (w, start) not in cache:
+                cache[(w, start)] = grads(start)
+            acc[l] += cache[(w, start)][l]
+            cnt[l] += 1
+        for l in range(L):
+            W[l] = W[l] - lr / max(1, cnt[l]) * acc[l]
+    return [w.float() for w in W]
 
 
 def selftest(iters=60):

@@ -123,6 +123,11 @@ class SyncReplicasMaster_NN(NN_Trainer):
         if self.resume:
             sd, step, mom = ckpt.load_checkpoint(self.resume)
             self.network.load_state_dict(sd)
+            if mom is not None:                 # optimizer state continues too (flat, parameters() order)
+                off = 0
+                for m in self.momentum_buffers:
+                    m.copy_(mom[off: off + m.numel()].view_as(m))
+                    off += m.numel()
             self.cur_step = step + 1
         return self
 
@@ -130,16 +135,16 @@ class SyncReplicasMaster_NN(NN_Trainer):
         from .parallel.b200_ps import B200ParameterServer
         from .parallel.delays import parse_delay_spec
         delay_fn = parse_delay_spec(self.inject_delay) if self.inject_delay else None
-        init_sd, self.step_offset = None, 0
+        init_sd, init_mom, self.step_offset = None, None, 0
         if self.resume:
             # the device protocol always counts from 1; the global step (checkpoint names) continues from the file
-            init_sd, self.step_offset, _ = ckpt.load_checkpoint(self.resume)
+            init_sd, self.step_offset, init_mom = ckpt.load_checkpoint(self.resume)
         self.ps = B200ParameterServer(self.network_config, self.batch_size, self.comm.Get_rank(), self.world_size, lr=self.lr,
                                       momentum=self.momentum, num_aggregate=self._should_kill_threshold, avg_mode=self.avg_mode,
                                       grad_dtype="bf16" if self.grad_dtype == "bf16" else "fp32", colocate=self.colocate or self.world_size == 1,
                                       n_buckets=self.n_buckets, seed=self.seed,
                                       deadline_ms=self.interval_ms if self.policy == "interval" else 0.0, delay_fn=delay_fn,
-                                      group=self.comm.group, device=self.comm.device, init_state_dict=init_sd)
+                                      group=self.comm.group, device=self.comm.device, init_state_dict=init_sd, init_momentum=init_mom)
         self.network = self.ps.net
         return self
 
@@ -173,6 +178,9 @@ class SyncReplicasMaster_NN(NN_Trainer):
                     if deadline is not None and time.monotonic() > deadline and len(complete_order) >= 1:
                         break
                     continue
+                if deadline is not None and time.monotonic() > deadline and len(complete_order) >= 1:
+                    self._rx_queue.put(item)    # belongs to whoever closes the next step (or is dropped there as stale)
+                    break
                 w, l, stamp = item[0], item[1], item[2]
                 if l < 0:
                     continue
@@ -329,7 +337,7 @@ class SyncReplicasMaster_NN(NN_Trainer):
         sd = self.network.state_dict()
         if self._pending_ckpt is not None:
             self._pending_ckpt.join()
-        mom = self.ps.momentum if self.ps is not None else None
+        mom = self.ps.momentum if self.ps is not None else torch.cat([m.reshape(-1) for m in self.momentum_buffers])
         path, th = ckpt.save_checkpoint(self.train_dir, self.cur_step, sd, mom, background=True)
         self._pending_ckpt = th
         return path

@@ -28,11 +28,14 @@ def save_checkpoint(train_dir: str, step: int, state_dict, momentum: Optional[to
     mom = None if momentum is None else momentum.detach().to("cpu", copy=True)
 
     def write():
+        # sidecar first, each through tmp + rename: a reader that sees model_step_N also sees its complete .optim
+        if mom is not None:
+            tmp = path + ".optim.tmp"
+            torch.save({"step": step, "momentum": mom}, tmp)
+            os.replace(tmp, path + ".optim")
         tmp = path + ".tmp"
         torch.save(cpu_sd, tmp)
         os.replace(tmp, path)
-        if mom is not None:
-            torch.save({"step": step, "momentum": mom}, path + ".optim")
 
     if background:
         t = threading.Thread(target=write, daemon=True)

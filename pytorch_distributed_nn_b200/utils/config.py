@@ -50,8 +50,9 @@ def kwargs_from_args(args, master: bool):
         "batch_size": args.batch_size, "learning_rate": args.lr, "max_epochs": args.epochs, "momentum": args.momentum,
         "network": args.network, "comm_method": getattr(args, "comm_type", "Bcast"),
     }
-    if master:
-        kw["kill_threshold"] = getattr(args, "num_aggregate", None)
+    # the reference hands k to the master only (distributed_nn.py:85-89); on the device backend every rank derives its
+    # data path (NVLS gather vs. pushed slots) from k and the deadline, so workers receive them too
+    kw["kill_threshold"] = getattr(args, "num_aggregate", None)
     for extra in ("max_steps", "train_dir", "eval_freq", "resume", "straggler_policy", "interval_ms", "avg_mode", "inject_delay",
                   "grad_dtype", "colocate_worker", "n_buckets", "log_interval", "seed", "evaluator"):
         if hasattr(args, extra):

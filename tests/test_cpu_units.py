@@ -167,7 +167,9 @@ def test_accuracy_and_flags():
     kw = kwargs_from_args(args, master=True)
     for key in ("batch_size", "learning_rate", "max_epochs", "momentum", "network", "comm_method", "kill_threshold"):
         assert key in kw
-    assert "kill_threshold" not in kwargs_from_args(args, master=False)
+    # workers get k and the deadline as well: on the device backend every rank derives its data path from them
+    kw_w = kwargs_from_args(args, master=False)
+    assert kw_w["kill_threshold"] == 5 and "interval_ms" in kw_w and "straggler_policy" in kw_w
 
 
 def test_engine_layout_matches_torch_parameter_order_on_meta_device():
