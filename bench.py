@@ -203,7 +203,7 @@ def main():
     import torch.distributed as dist
     from pytorch_distributed_nn_b200.ops import _lib
     from pytorch_distributed_nn_b200.parallel.b200_ps import B200ParameterServer
-    from pytorch_distributed_nn_b200.parallel.delays import parse_delay_spec
+    from pytorch_distributed_nn_b200.parallel.delays import DeviceDelay
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -215,21 +215,29 @@ def main():
         dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     B = args.batch_size
-    delay_fn = parse_delay_spec(args.inject_delay) if args.inject_delay else None
+    # straggler injection: sampled on the device (Philox keyed by seed/worker/step/layer), so it replays inside the CUDA graph
+    device_delay = DeviceDelay(args.inject_delay, seed=1) if args.inject_delay else None
     ps = B200ParameterServer(args.network, B, rank, world, lr=args.lr, momentum=args.momentum,
                              num_aggregate=args.num_aggregate or None, grad_dtype=args.grad_dtype, colocate=not (args.master_only and world > 1),
-                             n_buckets=args.n_buckets, delay_fn=delay_fn, group=group, device=dev, deadline_ms=args.interval_ms)
+                             n_buckets=args.n_buckets, device_delay=device_delay, group=group, device=dev, deadline_ms=args.interval_ms)
     chw = ps.net.in_chw
     gen = torch.Generator().manual_seed(1234 + rank)
     # synthetic CIFAR-10-shape data: raw 0..255 pixels like the reference reader (cifar10.py:167-199), 4 batches in rotation
-    host_x = [torch.empty(B, *chw).uniform_(0, 255, generator=gen).pin_memory() for _ in range(4)]
-    host_y = [torch.randint(0, 10, (B,), generator=gen).pin_memory() for _ in range(4)]
+    host_x = [torch.empty(B, *chw).uniform_(0, 255, generator=gen) for _ in range(4)]
+    host_y = [torch.randint(0, 10, (B,), generator=gen) for _ in range(4)]
     dev_x = [t.to(dev) for t in host_x]
     dev_y = [t.to(dev) for t in host_y]
-    stage_x = [torch.empty(B, *chw, device=dev) for _ in range(2)]
-    stage_y = [torch.empty(B, dtype=torch.long, device=dev) for _ in range(2)]
-    copy_stream = torch.cuda.Stream()
-    loss_host = torch.zeros(1).pin_memory()
+
+    class HostBatches:
+        """What a data set hands to the training loop: host tensors, one batch per call (utils/data.py next_batch contract)."""
+        i = 0
+
+        def next_batch(self, batch_size):
+            j = self.i % 4
+            self.i += 1
+            return host_x[j], host_y[j]
+
+    loader = HostBatches()
 
     def sync_all():
         torch.cuda.synchronize()
@@ -242,40 +250,16 @@ def main():
             ps.train_step(dev_x[i % 4], dev_y[i % 4])
 
     def run_e2e(n):
-        # input of step i+1 is copied on a side stream while step i computes; loss of every step is read back
-        ev_ready = [torch.cuda.Event(), torch.cuda.Event()]
-        ev_free = [torch.cuda.Event(), torch.cuda.Event()]
-        main = torch.cuda.current_stream()
-        with torch.cuda.stream(copy_stream):
-            stage_x[0].copy_(host_x[0], non_blocking=True)
-            stage_y[0].copy_(host_y[0], non_blocking=True)
-            ev_ready[0].record(copy_stream)
-        losses = []
-        for i in range(n):
-            cur, nxt = i % 2, (i + 1) % 2
-            if i + 1 < n:
-                with torch.cuda.stream(copy_stream):
-                    if i >= 1:
-                        copy_stream.wait_event(ev_free[nxt])
-                    stage_x[nxt].copy_(host_x[(i + 1) % 4], non_blocking=True)
-                    stage_y[nxt].copy_(host_y[(i + 1) % 4], non_blocking=True)
-                    ev_ready[nxt].record(copy_stream)
-            main.wait_event(ev_ready[cur])
-            loss = ps.train_step(stage_x[cur], stage_y[cur])
-            ev_free[cur].record(main)
-            if loss is not None:
-                loss_host.copy_(loss, non_blocking=True)
-            main.synchronize()            # the user reads the step's loss: a real D2H round trip per step
-            losses.append(float(loss_host))
-        return losses
+        """The public training loop (B200ParameterServer.fit, the one SyncReplicasMaster_NN / DistributedWorker run):
+        every step's batch goes host -> pinned -> device on a side stream, the loss of every step is read back."""
+        return ps.fit(loader if ps.is_worker else None, ps.step + n - 1, log_interval=1 << 30, cuda_graph=args.cuda_graph,
+                      graph_after=0, read_loss_every_step=True)
 
     # ---- warm-up (untimed) -------------------------------------------------------------------
     run_resident(2)
-    if args.cuda_graph and delay_fn is None:
-        # the whole step (wait, forward, loss, backward + bucket pushes, master kernel) becomes one graph launch
+    if args.cuda_graph:
+        # the whole step (wait, weight fetch, forward, loss, backward + bucket pushes, master kernels) becomes one graph launch
         ps.enable_cuda_graph(dev_x[0], dev_y[0])
-    else:
-        args.cuda_graph = False
     run_resident(args.warmup)
     run_e2e(max(1, min(args.warmup, 3)))
     sync_all()
@@ -286,6 +270,10 @@ def main():
 
     # ---- timed region 1: device-resident inputs ----------------------------------------------
     sync_all()
+    sets_before_resident = 0
+    if rank == 0:
+        ps.last_result()
+        sets_before_resident = ps.total_sets_applied
     _lib.reset_launch_count()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     per_step = []
@@ -295,10 +283,15 @@ def main():
     for i in range(args.steps):
         ps.train_step(dev_x[i % 4], dev_y[i % 4])
         evs[i + 1].record()
+    ps.join()                  # the master's stream: its last release belongs to the timed region
     e.record()
     sync_all()
     launches = _lib.launch_count()
     total_ms = s.elapsed_time(e)
+    sets_before_e2e = None
+    if rank == 0:
+        ps.last_result()
+        sets_after_resident = ps.total_sets_applied
     per_step_raw = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     per_step = sorted(per_step_raw)
     cdf = None
@@ -320,7 +313,8 @@ def main():
     sync_all()
     s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s2.record()
-    losses = run_e2e(args.steps)
+    losses = [v for _, v in run_e2e(args.steps)]
+    ps.join()
     e2.record()
     sync_all()
     e2e_ms = s2.elapsed_time(e2)
@@ -334,8 +328,12 @@ def main():
     res = ps.last_result() if rank == 0 else None
     if rank == 0:
         gb = B * ps.k            # images whose gradients are applied per step (k of n sets; k = n without stragglers)
-        value = gb * args.steps / (total_ms / 1e3)
-        e2e_value = gb * args.steps / (e2e_ms / 1e3)
+        ps.last_result()
+        # gradient sets the master actually applied (under the interval policy fewer than k may make a deadline)
+        sets_e2e = ps.total_sets_applied - sets_after_resident
+        sets_resident = sets_after_resident - sets_before_resident
+        value = B * sets_resident / (total_ms / 1e3)
+        e2e_value = B * sets_e2e / (e2e_ms / 1e3)
         h2d = B * chw[0] * chw[1] * chw[2] * 4 + B * 8
         out = {
             "metric": "images/sec (sync-SGD parameter server, whole job) + p50/p99 step ms",
@@ -351,11 +349,13 @@ def main():
                        "grad_wire_dtype": args.grad_dtype, "cuda_graph": bool(args.cuda_graph), "inject_delay": args.inject_delay or "none",
                        "l2_policy": "working set (activations >> 126 MB L2 at batch 1024; 4 input batches rotate) exceeds L2"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/sec", "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "final_loss": losses[-1]},
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "final_loss": losses[-1] if losses else None,
+                    "path": "B200ParameterServer.fit (the loop of the master / worker roles): pinned double-buffered H2D + loss D2H every step"},
             "gpu_launches": int(launches),
             "gpu_launches_per_step": round(launches / args.steps, 1),
+            "gradient_sets_applied": {"resident": sets_resident, "e2e": sets_e2e},
             "last_master_result": {"selected_mask": res[0], "kill_mask": res[1], "n_received": res[2], "step": res[3],
-                                   "device_timeline_us": ps.last_timing_us},
+                                   "bucket_masks": ps.last_bucket_masks, "device_timeline_us": ps.last_timing_us},
             "clocks": clocks,
         }
         if cdf is not None:

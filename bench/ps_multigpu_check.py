@@ -65,28 +65,38 @@ def run_case(network, batch, rank, world, steps, k, delay_spec, grad_dtype, colo
         if grad_dtype == "bf16":
             my_g = my_g.bfloat16().float()
         grads = gather_vec(my_g, world)
-        res = torch.zeros(4, device=dev, dtype=torch.int64)
+        res = torch.zeros(4 + 32, device=dev, dtype=torch.int64)
         if rank == 0:
-            res = torch.tensor(ps.last_result(), device=dev, dtype=torch.int64)
+            r4 = list(ps.last_result())
+            res = torch.tensor(r4 + ps.last_bucket_masks + [0] * (32 - len(ps.last_bucket_masks)), device=dev, dtype=torch.int64)
         dist.broadcast(res, 0)
-        sel, kill, nrecv, st = [int(v) for v in res.tolist()]
-        selected = [w for w in range(n_workers) if sel >> w & 1]
+        sel, kill, nrecv, st = [int(v) for v in res.tolist()[:4]]
+        bucket_masks = [int(v) for v in res.tolist()[4:]]
         # master copy vs oracle
         master_w = net.w32[:n].clone() if rank == 0 else torch.empty(n, device=dev)
         dist.broadcast(master_w, 0)
         if rank == 0:
             by_worker = {w: grads[ps._worker_rank(w)].cpu() for w in range(n_workers)}
-            w_ref, m_ref, sel_o, killed_o = kofn_update(w_ref, m_ref, by_worker, selected, len(selected), n_workers, lr=lr, mu=mu)
+            w_new, m_new = w_ref.clone(), m_ref.clone()
+            for b in net.buckets:       # every bucket is averaged over ITS first k arrivals
+                who = [w for w in range(n_workers) if bucket_masks[b.index] >> w & 1]
+                sl = slice(b.start, b.end)
+                w_new[sl], m_new[sl], _, _ = kofn_update(w_ref[sl], m_ref[sl], {w: g[sl] for w, g in by_worker.items()}, who, len(who),
+                                                         n_workers, lr=lr, mu=mu)
+                if len(who) != (k or n_workers):
+                    ok = False
+                    log.append(f"step {s}: bucket {b.index} averaged {len(who)} sets, expected {k or n_workers}")
+            w_ref, m_ref = w_new, m_new
             err = float((master_w.cpu() - w_ref).abs().max())
             # the in-switch bf16 reduction rounds the SUM to bf16 once more than the oracle does
             tol = 3e-4 if (ps.nvls_gather and grad_dtype == "bf16") else 2e-5
             if err > tol:
                 ok = False
                 log.append(f"step {s}: master vs oracle max abs err {err:.3e}")
-        # every worker's buffer == cast(master copy)
-        if ps.is_worker:
+        # every receiver's landing buffer of the next step's parity == cast(master copy)
+        if ps.is_worker or ps.is_listener:
             expect = master_w.to(net.w.dtype)
-            if not torch.equal(net.w[:n], expect):
+            if not torch.equal(ps.land[ps.step & 1][:n], expect):
                 ok = False
                 log.append(f"rank {rank} step {s}: weight buffer differs from the master broadcast")
         if st != s:

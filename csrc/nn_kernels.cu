@@ -26,6 +26,22 @@ static inline int grid_for(long long work_items, int threads, int max_blocks = 1
     return (int)b;
 }
 
+// Straggler abort guard of the layer kernels (BatchNorm, pooling, element-wise, loss): registered per host thread by
+// pdnn_set_abort_guard, passed to every launch; a CTA returns at once when *closed >= *step (the master closed the step
+// this worker is still computing). The decision is taken by one thread per CTA so that no __syncthreads() can be split.
+struct NnGuard { const uint32_t* closed; const uint32_t* step; };
+static thread_local NnGuard t_nn_guard = {nullptr, nullptr};
+static inline NnGuard nn_guard() { return t_nn_guard; }
+#define NN_GUARD_RETURN(g)                                                                         \
+    do {                                                                                           \
+        if ((g).closed != nullptr) {                                                               \
+            __shared__ int s_nn_abort;                                                             \
+            if (threadIdx.x == 0) s_nn_abort = ld_relaxed_sys((g).closed) >= ld_relaxed_sys((g).step); \
+            __syncthreads();                                                                       \
+            if (s_nn_abort) return;                                                                \
+        }                                                                                          \
+    } while (0)
+
 template <typename T> __device__ __forceinline__ float to_f(T v);
 template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
@@ -115,7 +131,8 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__
 // image staging (C <= 4, no padding): one thread per pixel -> every channel plane is read with full 128-byte warps and the
 // pixel's channels leave as one contiguous group
 template <typename T>
-__global__ void nchw_to_nhwc_pixel_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C, long long HW) {
+__global__ void nchw_to_nhwc_pixel_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C, long long HW, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const long long total = (long long)N * HW;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long n = i / HW;
@@ -225,7 +242,8 @@ __global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ col, int 
 }
 // vectorised variant: C % 8 == 0, Kpad == R*S*C, bf16
 __global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int H, int W,
-                                   int C, int R, int S, int stride, int pad, int OH, int OW) {
+                                   int C, int R, int S, int stride, int pad, int OH, int OW, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int C8 = C / 8;
     const long long total = (long long)N * OH * OW * R * S * C8;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -247,7 +265,8 @@ __global__ void im2col_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
 
 // stem-style im2col (C < 8): one thread produces 8 consecutive k of one row with a single 16-byte store.
 __global__ void im2col_rows8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int N, int H, int W, int C,
-                                    int R, int S, int stride, int pad, int OH, int OW, int Kpad) {
+                                    int R, int S, int stride, int pad, int OH, int OW, int Kpad, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int K = R * S * C;
     const int k8n = Kpad / 8;
     const long long total = (long long)N * OH * OW * k8n;
@@ -277,7 +296,8 @@ __global__ void im2col_rows8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bf
 
 // vectorised col2im: C % 8 == 0, one thread gathers 8 channels of one input pixel (16-byte loads).
 __global__ void col2im_vec8_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C,
-                                   int R, int S, int stride, int pad, int OH, int OW, int Kpad) {
+                                   int R, int S, int stride, int pad, int OH, int OW, int Kpad, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int C8 = C / 8;
     const long long total = (long long)N * H * W * C8;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -348,7 +368,8 @@ template <int MODE>   // 0: stats of x ; 1: backward sums (dz, dz*xhat), ReLU ma
 __global__ void __launch_bounds__(256, 2) bn_reduce_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
                                                         const __nv_bfloat16* __restrict__ dy, const float* __restrict__ mean_invstd,
                                                         float* __restrict__ out, long long M, int C, int relu,
-                                                        const float* __restrict__ gamma, const float* __restrict__ beta) {
+                                                        const float* __restrict__ gamma, const float* __restrict__ beta, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     extern __shared__ float sh[];   // [2][rows_per_iter][C]
     const int tpr = C / 8;                        // threads per row (<= 256)
     const int rpi = max(1, (int)blockDim.x / tpr); // rows per iteration
@@ -433,7 +454,8 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const __nv_bfloat16* 
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
                                                            float* __restrict__ mean_invstd, float* running_mean, float* running_var,
-                                                           long long M, int C, float eps, float momentum, int relu) {
+                                                           long long M, int C, float eps, float momentum, int relu, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int tpr = C / 8;
     const int rpi = max(1, (int)blockDim.x / tpr);
     const int ct = threadIdx.x % tpr;
@@ -498,7 +520,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
                                                            const float* __restrict__ gamma, const float* __restrict__ sums,
                                                            __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu,
-                                                           const float* __restrict__ beta) {
+                                                           const float* __restrict__ beta, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int tpr = C / 8;
     const int rpi = max(1, (int)blockDim.x / tpr);
     const int ct = threadIdx.x % tpr;
@@ -571,7 +594,8 @@ __global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ d
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         dx[i] = to_f<T>(y[i]) > 0.f ? dy[i] : from_f<T>(0.f);
 }
-__global__ void relu_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8) {
+__global__ void relu_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
         float v[8];
         load8(x + i * 8, v);
@@ -580,7 +604,8 @@ __global__ void relu_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_b
         store8(y + i * 8, v);
     }
 }
-__global__ void relu_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, long long n8) {
+__global__ void relu_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, long long n8, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
         float yv[8], dv[8];
         load8(y + i * 8, yv);
@@ -590,7 +615,8 @@ __global__ void relu_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ y, const 
         store8(dx + i * 8, dv);
     }
 }
-__global__ void add_vec8_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ o, long long n8, long long n) {
+__global__ void add_vec8_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ o, long long n8, long long n, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
         float av[8], bv[8];
         load8(a + i * 8, av);
@@ -604,7 +630,8 @@ __global__ void add_vec8_kernel(const __nv_bfloat16* __restrict__ a, const __nv_
 }
 
 template <typename T>
-__global__ void maxpool2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C) {
+__global__ void maxpool2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int OH = H / 2, OW = W / 2;
     const long long total = (long long)N * OH * OW * C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -618,7 +645,8 @@ __global__ void maxpool2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, 
 }
 // gradient goes to the first max of each window (torch semantics)
 template <typename T>
-__global__ void maxpool2_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, int N, int H, int W, int C) {
+__global__ void maxpool2_bwd_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, int N, int H, int W, int C, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int OH = H / 2, OW = W / 2;
     const long long total = (long long)N * OH * OW * C;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -649,7 +677,8 @@ __global__ void avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     }
 }
 // 8 channels per thread (C % 8 == 0): 16-byte accesses, one scale per vector instead of one division chain per element
-__global__ void avgpool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C8) {
+__global__ void avgpool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C8, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const long long total = (long long)N * C8;
     const float inv = 1.f / (float)HW;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -667,7 +696,8 @@ __global__ void avgpool_fwd_vec8_kernel(const __nv_bfloat16* __restrict__ x, __n
         store8(y + i * 8, acc);
     }
 }
-__global__ void avgpool_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C8) {
+__global__ void avgpool_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C8, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const long long total = (long long)N * HW * C8;
     const float inv = 1.f / (float)HW;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -692,7 +722,8 @@ __global__ void avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bf
 
 // column sums over rows (bias gradients). One block per 32-column strip, warps stride over rows.
 template <typename T>
-__global__ void __launch_bounds__(256) col_sum_kernel(const T* __restrict__ dy, long long ld, float* __restrict__ out, long long M, int C, int accumulate) {
+__global__ void __launch_bounds__(256) col_sum_kernel(const T* __restrict__ dy, long long ld, float* __restrict__ out, long long M, int C, int accumulate, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     __shared__ float sh[8][33];
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
     const int w = threadIdx.x >> 5;
@@ -715,7 +746,8 @@ __global__ void __launch_bounds__(256) col_sum_kernel(const T* __restrict__ dy, 
 template <typename T>
 __global__ void __launch_bounds__(256) cross_entropy_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
                                                             float* __restrict__ loss, T* __restrict__ dlogits, int* __restrict__ correct,
-                                                            int B, int classes, int ld) {
+                                                            int B, int classes, int ld, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -895,6 +927,12 @@ using namespace pdnn;
         return 0;                          \
     } while (0)
 
+extern "C" int pdnn_set_abort_guard(const uint32_t* closed, const uint32_t* step) {
+    t_nn_guard.closed = closed;
+    t_nn_guard.step = step;
+    return 0;
+}
+
 extern "C" int pdnn_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
     if (n <= 0) return 0;
     cast_f32_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, ST(stream)>>>(src, BF(dst), n);
@@ -907,7 +945,7 @@ extern "C" int pdnn_cast_bf16_to_f32(const void* src, float* dst, long long n, v
 }
 extern "C" int pdnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, void* stream) {
     if (C <= 4 && Cpad == C)
-        nchw_to_nhwc_pixel_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, (long long)H * W);
+        nchw_to_nhwc_pixel_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, (long long)H * W, nn_guard());
     else
         nchw_to_nhwc_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * Cpad, 256), 256, 0, ST(stream)>>>(x, BF(y), N, C, H, W, Cpad);
     LAUNCH_OK();
@@ -934,10 +972,10 @@ extern "C" int pdnn_im2col_bf16(const void* x, void* col, int N, int H, int W, i
                                 int OW, int Kpad, void* stream) {
     if (C % 8 == 0 && Kpad == R * S * C) {
         const long long total = (long long)N * OH * OW * R * S * (C / 8);
-        im2col_vec8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW);
+        im2col_vec8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, nn_guard());
     } else if (Kpad % 8 == 0) {
         const long long total = (long long)N * OH * OW * (Kpad / 8);
-        im2col_rows8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+        im2col_rows8_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad, nn_guard());
     } else {
         const long long total = (long long)N * OH * OW * Kpad;
         im2col_kernel<__nv_bfloat16><<<grid_for(total, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(x), BF(col), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
@@ -953,7 +991,7 @@ extern "C" int pdnn_im2col_f32(const float* x, float* col, int N, int H, int W, 
 extern "C" int pdnn_col2im_bf16(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad, int OH,
                                 int OW, int Kpad, void* stream) {
     if (C % 8 == 0 && Kpad % 8 == 0)
-        col2im_vec8_kernel<<<grid_for((long long)N * H * W * (C / 8), 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
+        col2im_vec8_kernel<<<grid_for((long long)N * H * W * (C / 8), 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad, nn_guard());
     else
         col2im_kernel<__nv_bfloat16><<<grid_for((long long)N * H * W * C, 256, 148 * 16), 256, 0, ST(stream)>>>(CBF(dcol), BF(dx), N, H, W, C, R, S, stride, pad, OH, OW, Kpad);
     LAUNCH_OK();
@@ -971,7 +1009,9 @@ static int resident_blocks(K kernel, int threads, size_t smem) {
     int per_sm = 0, dev = 0, sms = 148;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    return per_sm * sms;
+    // one SM's worth of slots stays free: a small kernel of another stream that is resident for the whole step (the
+    // parameter-server master's flag-polling warp) then costs nothing, instead of pushing one CTA into a second wave
+    return per_sm * sms - per_sm;
 }
 static int bn_reduce_cfg(int C, int* rpi, size_t* smem) {
     const int tpr = C / 8;
@@ -985,7 +1025,7 @@ extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C
     bn_reduce_cfg(C, &rpi, &smem);
     static const int wave = resident_blocks(bn_reduce_kernel<0>, 256, 16384);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, wave);
-    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
@@ -996,7 +1036,7 @@ extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float*
     bn_reduce_cfg(C, &rpi_a, &smem_a);
     static const int wave = resident_blocks(bn_fwd_apply_kernel, 256, 0);
     bn_fwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
-                                                                                     running_mean, running_var, M, C, eps, momentum, relu);
+                                                                                     running_mean, running_var, M, C, eps, momentum, relu, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums, long long M,
@@ -1008,9 +1048,9 @@ extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, 
     static const int wave1 = resident_blocks(bn_reduce_kernel<1>, 256, 16384), wave2 = resident_blocks(bn_reduce_kernel<2>, 256, 16384);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, (relu && y == nullptr) ? wave2 : wave1);
     if (relu && y == nullptr)
-        bn_reduce_kernel<2><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
+        bn_reduce_kernel<2><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard());
     else
-        bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta);
+        bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,
@@ -1022,16 +1062,16 @@ extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, c
     bn_reduce_cfg(C, &rpi_a, &smem_a);
     static const int wave = resident_blocks(bn_bwd_apply_kernel, 256, 0);
     bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
-                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu, beta);
+                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu, beta, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream) {
-    if (n % 8 == 0) relu_fwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n / 8);
+    if (n % 8 == 0) relu_fwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n / 8, nn_guard());
     else relu_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n);
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
-    if (n % 8 == 0) relu_bwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n / 8);
+    if (n % 8 == 0) relu_bwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n / 8, nn_guard());
     else relu_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n);
     LAUNCH_OK();
 }
@@ -1044,32 +1084,32 @@ extern "C" int pdnn_relu_bwd_f32(const float* y, const float* dy, float* dx, lon
     LAUNCH_OK();
 }
 extern "C" int pdnn_add_bf16(const void* a, const void* b, void* out, long long n, void* stream) {
-    add_vec8_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, ST(stream)>>>(CBF(a), CBF(b), BF(out), n / 8, n);
+    add_vec8_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, ST(stream)>>>(CBF(a), CBF(b), BF(out), n / 8, n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_maxpool2_fwd(const void* x, void* y, int N, int H, int W, int C, void* stream) {
-    maxpool2_fwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, H, W, C);
+    maxpool2_fwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, H, W, C, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_maxpool2_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, void* stream) {
-    maxpool2_bwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), BF(dx), N, H, W, C);
+    maxpool2_bwd_kernel<__nv_bfloat16><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), BF(dx), N, H, W, C, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_maxpool2_fwd_f32(const float* x, float* y, int N, int H, int W, int C, void* stream) {
-    maxpool2_fwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, N, H, W, C);
+    maxpool2_fwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, N, H, W, C, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_maxpool2_bwd_f32(const float* x, const float* y, const float* dy, float* dx, int N, int H, int W, int C, void* stream) {
-    maxpool2_bwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, dy, dx, N, H, W, C);
+    maxpool2_bwd_kernel<float><<<grid_for((long long)N * (H / 2) * (W / 2) * C, 256), 256, 0, ST(stream)>>>(x, y, dy, dx, N, H, W, C, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
-    if (C % 8 == 0) avgpool_fwd_vec8_kernel<<<grid_for((long long)N * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C / 8);
+    if (C % 8 == 0) avgpool_fwd_vec8_kernel<<<grid_for((long long)N * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C / 8, nn_guard());
     else avgpool_fwd_kernel<<<grid_for((long long)N * C, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), N, HW, C);
     LAUNCH_OK();
 }
 extern "C" int pdnn_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
-    if (C % 8 == 0) avgpool_bwd_vec8_kernel<<<grid_for((long long)N * HW * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C / 8);
+    if (C % 8 == 0) avgpool_bwd_vec8_kernel<<<grid_for((long long)N * HW * (C / 8), 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C / 8, nn_guard());
     else avgpool_bwd_kernel<<<grid_for((long long)N * HW * C, 256), 256, 0, ST(stream)>>>(CBF(dy), BF(dx), N, HW, C);
     LAUNCH_OK();
 }
@@ -1078,7 +1118,7 @@ extern "C" int pdnn_col_sum(const void* dy, long long ld, float* out, long long 
     if (gy > 64) gy = 64;
     if (gy < 1) gy = 1;
     if (gy > 1 && !accumulate) PDNN_CUDA_CHECK(cudaMemsetAsync(out, 0, sizeof(float) * C, ST(stream)));
-    col_sum_kernel<__nv_bfloat16><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(CBF(dy), ld, out, M, C, accumulate);
+    col_sum_kernel<__nv_bfloat16><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(CBF(dy), ld, out, M, C, accumulate, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_col_sum_f32(const float* dy, long long ld, float* out, long long M, int C, int accumulate, void* stream) {
@@ -1086,17 +1126,17 @@ extern "C" int pdnn_col_sum_f32(const float* dy, long long ld, float* out, long 
     if (gy > 64) gy = 64;
     if (gy < 1) gy = 1;
     if (gy > 1 && !accumulate) PDNN_CUDA_CHECK(cudaMemsetAsync(out, 0, sizeof(float) * C, ST(stream)));
-    col_sum_kernel<float><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(dy, ld, out, M, C, accumulate);
+    col_sum_kernel<float><<<dim3((C + 31) / 32, gy), 256, 0, ST(stream)>>>(dy, ld, out, M, C, accumulate, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_cross_entropy_fwd_bwd(const void* logits, const long long* labels, float* loss, void* dlogits, int* correct,
                                           int B, int classes, int ld, void* stream) {
-    cross_entropy_kernel<__nv_bfloat16><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(CBF(logits), labels, loss, BF(dlogits), correct, B, classes, ld);
+    cross_entropy_kernel<__nv_bfloat16><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(CBF(logits), labels, loss, BF(dlogits), correct, B, classes, ld, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_cross_entropy_fwd_bwd_f32(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
                                               int B, int classes, int ld, void* stream) {
-    cross_entropy_kernel<float><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(logits, labels, loss, dlogits, correct, B, classes, ld);
+    cross_entropy_kernel<float><<<grid_for((long long)B * 32, 256, 148), 256, 0, ST(stream)>>>(logits, labels, loss, dlogits, correct, B, classes, ld, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_topk_correct(const float* logits, const long long* labels, int B, int classes, int ld, const int* ks_host, int nk,
@@ -1205,10 +1245,10 @@ extern "C" int pdnn_bn_fwd_noalloc(const void* x, const float* gamma, const floa
     bn_reduce_cfg(C, &rpi, &smem);
     static const int wave = resident_blocks(bn_reduce_kernel<0>, 256, 16384);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, wave);
-    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr);
+    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr, NnGuard{nullptr, nullptr});
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     bn_fwd_apply_kernel<<<grid_for((M + rpi - 1) / rpi, 1, 148 * 8), 256, 0, ST(stream)>>>(
-        CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd, running_mean, running_var, M, C, eps, momentum, relu);
+        CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd, running_mean, running_var, M, C, eps, momentum, relu, NnGuard{nullptr, nullptr});
     LAUNCH_OK();
 }

@@ -13,8 +13,6 @@
 
 namespace pdnn {
 
-// control words of the master (zero-initialised by the caller once)
-enum { CTL_MASK = 0, CTL_MASK_STEP = 1, CTL_DONE = 2, CTL_NSEL = 3, CTL_ERR = 4, CTL_PUSH_DONE = 8 };
 
 #ifndef PDNN_PS_HARD_TIMEOUT_NS
 #define PDNN_PS_HARD_TIMEOUT_NS 30000000000ull   // a master that never sees k gradients gives up after 30 s
@@ -74,8 +72,20 @@ __global__ void __launch_bounds__(512) ps_push_kernel(const float* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
-// master: select first k, kill the rest, reduce + momentum SGD + broadcast
+// master: per gradient bucket, in arrival order: take the first k arrivals, reduce + 1/k + momentum SGD +
+// cast + broadcast; the last bucket also decides the kill set and releases the workers.
+//
+// The reference sums every message the moment Waitany returns it (sync_replicas_master_nn.py:148-166; C++
+// sync_replicas_master_nn.h:71-101) and its kill decision is taken on the k-th arrival of parameter 0, the last
+// gradient a worker produces (:172-187). Here a step is n_buckets x {wait kernel, reduce kernel} on the master's
+// own stream: bucket b (deepest layers first) is reduced, applied and broadcast while the workers are still
+// running the backward pass of the shallower layers, so only the last (shallowest) bucket sits on the critical
+// path after the k-th worker finishes. New weights land in a parity buffer (step & 1) that no worker reads
+// before the step is released, so updating bucket b mid-backward cannot disturb a worker that still needs the
+// old weights for its data gradients.
 // ------------------------------------------------------------------------------------------------
+enum { CTL_DONE = 2, CTL_ERR = 4, CTL_TOTAL = 6, CTL_T0 = 8, CTL_TK = 10, CTL_BMASK = 64, CTL_BCNT = 128 };
+
 struct MasterArgs {
     pdnn_ps_master_t a;
     uint32_t* result;
@@ -86,184 +96,220 @@ __device__ __forceinline__ void multimem_st_v4(void* mc_addr, uint4 v) {
                  "r"(v.z), "r"(v.w)
                  : "memory");
 }
+__device__ __forceinline__ void multimem_st_v2(void* mc_addr, uint2 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc_addr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_u64(const uint32_t* p) { return (uint64_t)p[0] | ((uint64_t)p[1] << 32); }
+__device__ __forceinline__ void st_u64(uint32_t* p, uint64_t v) { p[0] = (uint32_t)v; p[1] = (uint32_t)(v >> 32); }
 
-__global__ void __launch_bounds__(512) ps_master_step_kernel(const __grid_constant__ MasterArgs margs) {
+// One warp: lane w polls worker w's arrival word of bucket b; arrivals are admitted in the order they are seen
+// (simultaneous ones by rank) until k are in. <<<1, 32>>>
+__global__ void __launch_bounds__(32) ps_bucket_wait_kernel(const __grid_constant__ MasterArgs margs, int b, int is_first, int is_last) {
     const pdnn_ps_master_t& a = margs.a;
-    // CUDA-graph mode: the step to close is read from device memory (and advanced by the last block below)
     const uint32_t cur_step = a.step_ptr != nullptr ? ld_relaxed_sys(a.step_ptr) : a.step;
-    __shared__ uint32_t s_mask;
-    __shared__ uint32_t s_nsel;
     uint32_t* ctl = a.control;
-
-    // -------- phase A: decide the contributing set (one thread of block 0), everyone else waits locally
-    if (threadIdx.x == 0) {
-        if (blockIdx.x == 0) {
-            const uint64_t t0 = globaltimer_ns();
-            uint32_t mask = 0, count = 0, err = 0;
-            const uint32_t want = (uint32_t)a.k;
-            for (;;) {
-                for (int w = 0; w < a.n_workers && count < want; ++w) {
-                    if (!(mask & (1u << w)) && ld_acquire_sys(a.arrival_flags + w) == cur_step) {
-                        mask |= 1u << w;
-                        ++count;
-                    }
-                }
-                if (count >= want) break;
-                const uint64_t el = globaltimer_ns() - t0;
-                if (a.deadline_ns > 0 && el > (uint64_t)a.deadline_ns && count > 0) break;   // interval policy
-                if (el > PDNN_PS_HARD_TIMEOUT_NS) { err = 1; break; }
-                __nanosleep(200);
-            }
-            // straggler kill: tell every worker outside the set that this step is closed
-            uint32_t kill = 0;
-            for (int w = 0; w < a.n_workers; ++w) {
-                if (!(mask & (1u << w))) {
-                    kill |= 1u << w;
-                    if (a.worker_closed[w] != nullptr) st_release_sys(a.worker_closed[w], cur_step);
-                }
-            }
-            ctl[CTL_NSEL] = count;
-            ctl[CTL_ERR] = err;
+    const int lane = threadIdx.x;
+    uint64_t t0;
+    if (is_first) {
+        t0 = globaltimer_ns();
+        t0 = __shfl_sync(0xffffffffu, t0, 0);
+        if (lane == 0) st_u64(ctl + CTL_T0, t0);
+    } else {
+        t0 = ld_u64(ctl + CTL_T0);
+    }
+    const uint32_t* flag = a.arrival_flags + (long long)lane * a.arrival_stride + b;
+    const uint32_t want = (uint32_t)a.k;
+    uint32_t mask = 0, err = 0, polls = 0;
+    const uint32_t sleep_ns = a.poll_sleep_ns > 0 ? (uint32_t)a.poll_sleep_ns : 400u;
+    uint64_t now = t0;
+    for (;;) {
+        // relaxed polling (served by L2, no L1 invalidation on this SM, which other streams' CTAs share); one system-scope
+        // fence after the loop orders the slot reads of the reduce kernel behind the flags seen here
+        const bool arrived = lane < a.n_workers && !((mask >> lane) & 1u) && ld_relaxed_sys(flag) == cur_step;
+        uint32_t m = __ballot_sync(0xffffffffu, arrived);
+        while (m != 0 && (uint32_t)__popc(mask) < want) {
+            mask |= m & (0u - m);     // lowest set bit
+            m &= m - 1;
+        }
+        if ((uint32_t)__popc(mask) >= want) { now = __shfl_sync(0xffffffffu, globaltimer_ns(), 0); break; }
+        if ((++polls & 15u) != 0u && a.deadline_ns == 0) { __nanosleep(sleep_ns); continue; }   // the clock is read every 16th poll
+        now = __shfl_sync(0xffffffffu, globaltimer_ns(), 0);
+        const uint64_t el = now - t0;
+        if (a.deadline_ns > 0 && el > (uint64_t)a.deadline_ns && mask != 0) break;      // interval policy
+        if (el > (a.hard_timeout_ns > 0 ? (uint64_t)a.hard_timeout_ns : PDNN_PS_HARD_TIMEOUT_NS)) { err = 1; break; }
+        __nanosleep(sleep_ns);
+    }
+    __threadfence_system();
+    const uint32_t count = (uint32_t)__popc(mask);
+    if (is_last && lane < a.n_workers && !((mask >> lane) & 1u) && a.worker_closed[lane] != nullptr)
+        st_release_sys(a.worker_closed[lane], cur_step);          // straggler kill: this step is closed for you
+    if (lane == 0) {
+        ctl[CTL_BMASK + b] = err ? 0u : mask;
+        ctl[CTL_BCNT + b] = err ? 0u : count;
+        if (err) ctl[CTL_ERR] = 1;
+        margs.result[8 + b] = mask;
+        margs.result[40 + b] = (uint32_t)((now - t0) / 1000ull);
+        if (is_last) {
+            const uint32_t all = a.n_workers >= 32 ? 0xffffffffu : ((1u << a.n_workers) - 1u);
+            const uint32_t bad = ctl[CTL_ERR];
             margs.result[0] = mask;
-            margs.result[1] = kill;
+            margs.result[1] = all & ~mask;
             margs.result[2] = count;
-            margs.result[3] = err ? 0xDEADu : cur_step;
-            // device-side timeline (globaltimer, microseconds): how long the master waited for the k-th arrival
-            const uint64_t t1 = globaltimer_ns();
-            margs.result[4] = (uint32_t)((t1 - t0) / 1000ull);
-            ctl[5] = (uint32_t)(t1 / 1000ull);
-            ctl[CTL_MASK] = mask;
-            __threadfence();
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ctl + CTL_MASK_STEP), "r"(cur_step) : "memory");
-            s_mask = mask;
-            s_nsel = count;
-        } else {
-            while (ld_acquire_gpu(ctl + CTL_MASK_STEP) != cur_step) __nanosleep(100);
-            s_mask = ctl[CTL_MASK];
-            s_nsel = ctl[CTL_NSEL];
+            margs.result[3] = (err || bad) ? 0xDEADu : cur_step;
+            margs.result[4] = (uint32_t)((now - t0) / 1000ull);   // step start -> k-th arrival of the last bucket
+            margs.result[7] = (uint32_t)a.n_buckets;
+            ctl[CTL_TOTAL] += count;
+            margs.result[6] = ctl[CTL_TOTAL];                     // gradient sets applied since the start of the run
+            st_u64(ctl + CTL_TK, now);
         }
     }
-    __syncthreads();
-    const uint32_t mask = s_mask;
-    const uint32_t nsel = s_nsel;
+}
 
-    // -------- phase B: reduce selected slots in rank order, 1/k, momentum SGD, cast, broadcast
+template <bool BF16_SLOT>
+__device__ __forceinline__ float4 ps_load_sum(const pdnn_ps_master_t& a, uint32_t mask, bool in_switch, long long i) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (in_switch) {
+        // every worker contributes: one load-reduce through the NVLS multicast address sums the workers' local slots
+        // inside the switch (1x ingress instead of n x)
+        if (BF16_SLOT) {
+            uint32_t r0, r1;
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0, %1}, [%2];"
+                         : "=r"(r0), "=r"(r1)
+                         : "l"(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots) + i * 4)
+                         : "memory");
+            const float2 lo = unpack_bf16x2(r0), hi = unpack_bf16x2(r1);
+            acc = make_float4(lo.x, lo.y, hi.x, hi.y);
+        } else {
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(acc.x), "=f"(acc.y), "=f"(acc.z), "=f"(acc.w)
+                         : "l"(reinterpret_cast<const float*>(a.multicast_slots) + i * 4)
+                         : "memory");
+        }
+        return acc;
+    }
+    for (int w = 0; w < a.n_workers; ++w) {       // rank order: deterministic sum
+        if (!((mask >> w) & 1u)) continue;
+        if (BF16_SLOT) {
+            const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w]) + i * 4);
+            const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
+            acc.x += lo.x; acc.y += lo.y; acc.z += hi.x; acc.w += hi.y;
+        } else {
+            const float4 g = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.slots[w]) + i * 4);
+            acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+        }
+    }
+    return acc;
+}
+
+template <bool BF16_SLOT>
+__device__ __forceinline__ void ps_poison(const pdnn_ps_master_t& a, uint32_t mask, bool in_switch, long long i) {
+    if (in_switch) {
+        if (BF16_SLOT) multimem_st_v2(const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots)) + i * 4,
+                                      make_uint2(0x7FC07FC0u, 0x7FC07FC0u));
+        else multimem_st_v4(const_cast<float*>(reinterpret_cast<const float*>(a.multicast_slots)) + i * 4,
+                            make_uint4(0x7FC00000u, 0x7FC00000u, 0x7FC00000u, 0x7FC00000u));
+        return;
+    }
+    for (int w = 0; w < a.n_workers; ++w) {
+        if (!((mask >> w) & 1u)) continue;
+        if (BF16_SLOT)
+            *reinterpret_cast<uint2*>(const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w])) + i * 4) =
+                make_uint2(0x7FC07FC0u, 0x7FC07FC0u);
+        else
+            *reinterpret_cast<uint4*>(const_cast<float*>(reinterpret_cast<const float*>(a.slots[w])) + i * 4) =
+                make_uint4(0x7FC00000u, 0x7FC00000u, 0x7FC00000u, 0x7FC00000u);
+    }
+}
+
+// Reduce + update + broadcast of elements [lo, hi) (multiples of 4). Each thread keeps PS_UNROLL independent
+// gradient loads in flight (one multimem.ld_reduce round trip through the switch is ~2 us).
+#define PS_UNROLL 4
+template <bool BF16_SLOT>
+__global__ void __launch_bounds__(512) ps_bucket_reduce_kernel(const __grid_constant__ MasterArgs margs, int b, int is_last) {
+    const pdnn_ps_master_t& a = margs.a;
+    const uint32_t cur_step = a.step_ptr != nullptr ? ld_relaxed_sys(a.step_ptr) : a.step;
+    uint32_t* ctl = a.control;
+    const uint32_t mask = ctl[CTL_BMASK + b];      // written by the wait kernel that precedes this launch in the stream
+    const uint32_t nsel = ctl[CTL_BCNT + b];
     if (nsel > 0) {
-        float scale;
-        if (a.avg_mode == 1) scale = 1.f / (float)a.n_workers;
-        else scale = 1.f / (float)nsel;
-        const long long n4 = a.n / 4;
+        const float scale = a.avg_mode == 1 ? 1.f / (float)a.n_workers : 1.f / (float)nsel;
+        const bool in_switch = a.multicast_slots != nullptr && nsel == (uint32_t)a.n_workers;
+        const int par = (int)((cur_step + 1u) & 1u);            // weights of step s+1 land in parity (s+1) & 1
+        void* mcw = a.multicast_weights[par];
+        const long long i0 = a.bucket_lo[b] / 4, i1 = a.bucket_hi[b] / 4;
         const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
         const long long nth = (long long)gridDim.x * blockDim.x;
-        for (long long i = tid; i < n4; i += nth) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (a.multicast_slots != nullptr && nsel == (uint32_t)a.n_workers) {
-                // all n sets contribute: one load-reduce through the NVLS multicast address sums the workers' local
-                // slots inside the switch (1x ingress instead of n x)
-                if (a.slot_is_bf16) {
-                    uint32_t r0, r1;
-                    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v2.bf16x2 {%0, %1}, [%2];"
-                                 : "=r"(r0), "=r"(r1)
-                                 : "l"(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots) + i * 4)
-                                 : "memory");
-                    const float2 lo = unpack_bf16x2(r0), hi = unpack_bf16x2(r1);
-                    acc = make_float4(lo.x, lo.y, hi.x, hi.y);
-                } else {
-                    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                                 : "=f"(acc.x), "=f"(acc.y), "=f"(acc.z), "=f"(acc.w)
-                                 : "l"(reinterpret_cast<const float*>(a.multicast_slots) + i * 4)
-                                 : "memory");
-                }
-                if (a.poison_slots) {      // one multicast store poisons this element in every worker's local slot
-                    if (a.slot_is_bf16)
-                        asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(
-                                         const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.multicast_slots)) + i * 4),
-                                     "r"(0x7FC07FC0u), "r"(0x7FC07FC0u) : "memory");
-                    else
-                        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(
-                                         const_cast<float*>(reinterpret_cast<const float*>(a.multicast_slots)) + i * 4),
-                                     "r"(0x7FC00000u), "r"(0x7FC00000u), "r"(0x7FC00000u), "r"(0x7FC00000u) : "memory");
-                }
-            } else
-            for (int w = 0; w < a.n_workers; ++w) {
-                if (!(mask & (1u << w))) continue;
-                if (a.slot_is_bf16) {
-                    const uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w]) + i * 4);
-                    const float2 lo = unpack_bf16x2(u.x), hi = unpack_bf16x2(u.y);
-                    acc.x += lo.x; acc.y += lo.y; acc.z += hi.x; acc.w += hi.y;
-                    if (a.poison_slots)
-                        *reinterpret_cast<uint2*>(const_cast<__nv_bfloat16*>(reinterpret_cast<const __nv_bfloat16*>(a.slots[w])) + i * 4) =
-                            make_uint2(0x7FC07FC0u, 0x7FC07FC0u);
-                } else {
-                    const float4 g = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(a.slots[w]) + i * 4);
-                    acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
-                    if (a.poison_slots)
-                        *reinterpret_cast<uint4*>(const_cast<float*>(reinterpret_cast<const float*>(a.slots[w])) + i * 4) =
-                            make_uint4(0x7FC00000u, 0x7FC00000u, 0x7FC00000u, 0x7FC00000u);
-                }
+        const float lr = a.lr, mu = a.mu;
+        for (long long base = i0 + tid; base < i1; base += nth * PS_UNROLL) {
+            float4 acc[PS_UNROLL];
+#pragma unroll
+            for (int u = 0; u < PS_UNROLL; ++u) {
+                const long long i = base + u * nth;
+                if (i < i1) acc[u] = ps_load_sum<BF16_SLOT>(a, mask, in_switch, i);
             }
-            float4 m = reinterpret_cast<float4*>(a.momentum)[i];
-            float4 wv = reinterpret_cast<float4*>(a.master_w)[i];
-            m.x = a.mu * m.x + scale * acc.x; m.y = a.mu * m.y + scale * acc.y;
-            m.z = a.mu * m.z + scale * acc.z; m.w = a.mu * m.w + scale * acc.w;
-            wv.x -= a.lr * m.x; wv.y -= a.lr * m.y; wv.z -= a.lr * m.z; wv.w -= a.lr * m.w;
-            reinterpret_cast<float4*>(a.momentum)[i] = m;
-            reinterpret_cast<float4*>(a.master_w)[i] = wv;
-            if (a.weights_are_bf16) {
-                uint2 u;
-                u.x = pack_bf16x2(wv.x, wv.y); u.y = pack_bf16x2(wv.z, wv.w);
-                if (a.multicast_weights != nullptr) {
-                    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(
-                                     reinterpret_cast<__nv_bfloat16*>(a.multicast_weights) + i * 4),
-                                 "r"(u.x), "r"(u.y)
-                                 : "memory");
+#pragma unroll
+            for (int u = 0; u < PS_UNROLL; ++u) {
+                const long long i = base + u * nth;
+                if (i >= i1) continue;
+                if (a.poison_slots) ps_poison<BF16_SLOT>(a, mask, in_switch, i);
+                float4 m = reinterpret_cast<float4*>(a.momentum)[i];
+                float4 wv = reinterpret_cast<float4*>(a.master_w)[i];
+                m.x = mu * m.x + scale * acc[u].x; m.y = mu * m.y + scale * acc[u].y;
+                m.z = mu * m.z + scale * acc[u].z; m.w = mu * m.w + scale * acc[u].w;
+                wv.x -= lr * m.x; wv.y -= lr * m.y; wv.z -= lr * m.z; wv.w -= lr * m.w;
+                reinterpret_cast<float4*>(a.momentum)[i] = m;
+                reinterpret_cast<float4*>(a.master_w)[i] = wv;
+                if (a.weights_are_bf16) {
+                    uint2 u2;
+                    u2.x = pack_bf16x2(wv.x, wv.y); u2.y = pack_bf16x2(wv.z, wv.w);
+                    if (mcw != nullptr) {
+                        multimem_st_v2(reinterpret_cast<__nv_bfloat16*>(mcw) + i * 4, u2);
+                    } else {
+                        for (int r = 0; r < a.n_receivers; ++r)
+                            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(a.recv_weights[par][r]) + i * 4) = u2;
+                    }
                 } else {
-                    for (int w = 0; w < a.n_workers; ++w)
-                        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(a.worker_weights[w]) + i * 4) = u;
-                }
-            } else {
-                uint4 u = *reinterpret_cast<uint4*>(&wv);
-                if (a.multicast_weights != nullptr) {
-                    multimem_st_v4(reinterpret_cast<float*>(a.multicast_weights) + i * 4, u);
-                } else {
-                    for (int w = 0; w < a.n_workers; ++w) st_na_v4(reinterpret_cast<float*>(a.worker_weights[w]) + i * 4, u);
-                }
-            }
-        }
-        if (tid == 0) {
-            for (long long j = n4 * 4; j < a.n; ++j) {
-                float acc = 0.f;
-                for (int w = 0; w < a.n_workers; ++w) {
-                    if (!(mask & (1u << w))) continue;
-                    acc += a.slot_is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(a.slots[w])[j])
-                                          : reinterpret_cast<const float*>(a.slots[w])[j];
-                }
-                float m = a.mu * a.momentum[j] + scale * acc;
-                a.momentum[j] = m;
-                const float wv = a.master_w[j] - a.lr * m;
-                a.master_w[j] = wv;
-                for (int w = 0; w < a.n_workers; ++w) {
-                    if (a.weights_are_bf16) reinterpret_cast<__nv_bfloat16*>(a.worker_weights[w])[j] = __float2bfloat16(wv);
-                    else reinterpret_cast<float*>(a.worker_weights[w])[j] = wv;
+                    const uint4 u4 = *reinterpret_cast<uint4*>(&wv);
+                    if (mcw != nullptr) {
+                        multimem_st_v4(reinterpret_cast<float*>(mcw) + i * 4, u4);
+                    } else {
+                        for (int r = 0; r < a.n_receivers; ++r) st_na_v4(reinterpret_cast<float*>(a.recv_weights[par][r]) + i * 4, u4);
+                    }
                 }
             }
         }
     }
-
-    // -------- phase C: grid completion, then release every worker with step+1
+    if (!is_last) return;
+    // -------- grid completion of the last bucket, then release every receiver with step+1
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence_system();
         const uint32_t done = atom_add_acqrel_gpu(ctl + CTL_DONE, 1u) + 1u;
         if (done == gridDim.x) {
             ctl[CTL_DONE] = 0;
-            margs.result[5] = (uint32_t)(globaltimer_ns() / 1000ull) - ctl[5];   // reduce + update + broadcast, microseconds
+            ctl[CTL_ERR] = 0;
+            margs.result[5] = (uint32_t)((globaltimer_ns() - ld_u64(ctl + CTL_TK)) / 1000ull);   // k-th arrival -> release
             if (a.step_ptr != nullptr) st_relaxed_sys(a.step_ptr, cur_step + 1u);
             __threadfence_system();
-            for (int w = 0; w < a.n_workers; ++w)
-                if (a.worker_ready[w] != nullptr) st_release_sys(a.worker_ready[w], cur_step + 1u);
+            for (int r = 0; r < a.n_receivers; ++r)
+                if (a.recv_ready[r] != nullptr) st_release_sys(a.recv_ready[r], cur_step + 1u);
         }
     }
+}
+
+// Worker: copy the landing buffer of this step (parity step & 1) into the private compute copy.
+__global__ void __launch_bounds__(512) ps_fetch_kernel(const uint4* __restrict__ land0, const uint4* __restrict__ land1,
+                                                       uint4* __restrict__ dst, long long n16, const uint32_t* step_word, uint32_t step) {
+    if (step_word != nullptr) step = ld_relaxed_sys(step_word);
+    const uint4* src = (step & 1u) ? land1 : land0;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    long long i = tid;
+    for (; i + 3 * nth < n16; i += 4 * nth) {
+        const uint4 a = src[i], b = src[i + nth], c = src[i + 2 * nth], d = src[i + 3 * nth];
+        dst[i] = a; dst[i + nth] = b; dst[i + 2 * nth] = c; dst[i + 3 * nth] = d;
+    }
+    for (; i < n16; i += nth) dst[i] = src[i];
 }
 
 __global__ void ps_wait_flag_kernel(const uint32_t* flag, uint32_t value, uint32_t* cur_step_word, long long timeout_ns,
@@ -293,6 +339,49 @@ __global__ void ps_delay_kernel(long long ns, const uint32_t* guard_closed, cons
     const uint64_t t0 = globaltimer_ns();
     while (globaltimer_ns() - t0 < (uint64_t)ns) {
         if (guard_closed != nullptr && ld_relaxed_sys(guard_closed) >= ld_relaxed_sys(guard_step)) break;
+        __nanosleep(500);
+    }
+}
+
+// Straggler injection sampled ON the device: the draw is a pure function of (seed, worker, step, layer) through
+// Philox4x32-10, the step comes from the worker's device-side step word, so the launch is identical every step and can
+// be replayed from a CUDA graph (the reference sleeps on the host: pure_py_code/distributed_worker.py:130-132 before
+// every backward layer; distributed_TF/src/distributed_train.py:288-290 uniform 300..1200 ms per step).
+__device__ __forceinline__ void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c[0], p1 = (uint64_t)0xCD9E8D57u * c[2];
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0, n1 = (uint32_t)p1, n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1, n3 = (uint32_t)p0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+
+__global__ void ps_delay_sampled_kernel(const __grid_constant__ pdnn_delay_spec_t sp, int worker, int layer, const uint32_t* step_word,
+                                        const uint32_t* guard_closed, uint32_t* log_ns) {
+    const uint32_t step = ld_relaxed_sys(step_word);
+    uint32_t c[4] = {step, (uint32_t)layer, 0u, 0u};
+    philox4x32_10(c, (uint32_t)sp.seed, (uint32_t)(sp.seed >> 32) ^ ((uint32_t)worker * 0x9E3779B9u));
+    const float u0 = (float)(c[0] >> 8) * (1.0f / 16777216.0f), u1 = (float)(c[1] >> 8) * (1.0f / 16777216.0f);
+    const float u2 = (float)(c[2] >> 8) * (1.0f / 16777216.0f);
+    float ms = 0.f;
+    const bool hit = (sp.rank_mask == 0ull || ((sp.rank_mask >> (worker + 1)) & 1ull)) && (sp.prob >= 1.0f || u0 < sp.prob);
+    if (hit) {
+        switch (sp.kind) {
+            case 1: ms = sp.a; break;
+            case 2: ms = sp.a + (sp.b - sp.a) * u1; break;
+            case 3: ms = sp.a - sp.b * logf(1.0f - u1); break;
+            case 4: ms = expf(sp.a + sp.b * sqrtf(-2.0f * logf(1.0f - u1)) * cospif(2.0f * u2)); break;
+            case 5: ms = sp.a * powf(1.0f - u1, -1.0f / sp.b); break;
+            default: break;
+        }
+    }
+    const float nsf = fmaxf(ms, 0.f) * sp.scale * 1e6f;
+    const uint64_t ns = (uint64_t)nsf;
+    if (log_ns != nullptr) log_ns[layer] = (uint32_t)(ns > 0xffffffffull ? 0xffffffffull : ns);
+    const uint64_t t0 = globaltimer_ns();
+    while (globaltimer_ns() - t0 < ns) {
+        if (guard_closed != nullptr && ld_relaxed_sys(guard_closed) >= step) break;      // the step was closed: stop waiting
         __nanosleep(500);
     }
 }
@@ -373,15 +462,47 @@ extern "C" int pdnn_ps_push_dev(const float* grad, void* slot_peer, long long n,
 extern "C" int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* stream) {
     PDNN_REQUIRE(args != nullptr && result != nullptr, "ps_master_step: null arguments");
     PDNN_REQUIRE(args->n_workers >= 1 && args->n_workers <= PDNN_MAX_WORKERS, "ps_master_step: n_workers=%d out of range", args->n_workers);
+    PDNN_REQUIRE(args->n_receivers >= 0 && args->n_receivers <= PDNN_MAX_RECEIVERS, "ps_master_step: n_receivers=%d out of range", args->n_receivers);
     PDNN_REQUIRE(args->k >= 1 && args->k <= args->n_workers, "ps_master_step: k=%d must be in [1, %d]", args->k, args->n_workers);
     PDNN_REQUIRE(args->control != nullptr && args->master_w != nullptr && args->momentum != nullptr, "ps_master_step: missing buffers");
-    PDNN_REQUIRE(args->n % 4 == 0 || (args->multicast_weights == nullptr && args->multicast_slots == nullptr),
-                 "ps_master_step: multicast paths need n %% 4 == 0");
+    PDNN_REQUIRE(args->n_buckets >= 1 && args->n_buckets <= PDNN_MAX_BUCKETS, "ps_master_step: n_buckets=%d out of range", args->n_buckets);
+    PDNN_REQUIRE(args->arrival_stride >= args->n_buckets, "ps_master_step: arrival_stride %d < n_buckets %d", args->arrival_stride, args->n_buckets);
+    for (int b = 0; b < args->n_buckets; ++b)
+        PDNN_REQUIRE(args->bucket_lo[b] >= 0 && args->bucket_hi[b] > args->bucket_lo[b] && args->bucket_hi[b] <= args->n &&
+                         args->bucket_lo[b] % 4 == 0 && args->bucket_hi[b] % 4 == 0,
+                     "ps_master_step: bucket %d = [%lld, %lld) must be a non-empty 4-element-aligned range inside [0, %lld)", b,
+                     args->bucket_lo[b], args->bucket_hi[b], args->n);
+    for (int b = 0; b < args->n_buckets; ++b)
+        if (int rc = pdnn_ps_master_bucket(args, result, b, stream)) return rc;
+    return 0;
+}
+
+// One bucket of a master step (see pdnn_ps_master_step, which is the loop over all of them; arguments validated there).
+// A caller that knows when bucket b can first be complete (the colocated worker has just pushed its own share) can
+// enqueue the buckets one by one behind that point, so that the polling warp is resident for the skew between the
+// workers only, not for the whole backward pass.
+extern "C" int pdnn_ps_master_bucket(const pdnn_ps_master_t* args, uint32_t* result, int b, void* stream) {
+    PDNN_REQUIRE(args != nullptr && result != nullptr && b >= 0 && b < args->n_buckets, "ps_master_bucket: bad arguments");
     MasterArgs m;
     m.a = *args;
     m.result = result;
-    const int grid = ps_grid(args->n / 4 + 1, 512, args->max_ctas);
-    ps_master_step_kernel<<<grid, 512, 0, ST(stream)>>>(m);
+    const int last = b == args->n_buckets - 1;
+    ps_bucket_wait_kernel<<<1, 32, 0, ST(stream)>>>(m, b, b == 0, last);
+    PDNN_COUNT_LAUNCH();
+    const int grid = ps_grid((args->bucket_hi[b] - args->bucket_lo[b]) / 4 / PS_UNROLL + 1, 512, args->max_ctas);
+    if (args->slot_is_bf16) ps_bucket_reduce_kernel<true><<<grid, 512, 0, ST(stream)>>>(m, b, last);
+    else ps_bucket_reduce_kernel<false><<<grid, 512, 0, ST(stream)>>>(m, b, last);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pdnn_ps_fetch_weights(const void* land0, const void* land1, void* dst, long long nbytes, const uint32_t* step_word,
+                                     uint32_t step, void* stream) {
+    PDNN_REQUIRE(nbytes > 0 && nbytes % 16 == 0, "ps_fetch_weights: size must be a positive multiple of 16 bytes");
+    const int grid = ps_grid(nbytes / 16 / 4 + 1, 512, 148 * 2);
+    ps_fetch_kernel<<<grid, 512, 0, ST(stream)>>>(reinterpret_cast<const uint4*>(land0), reinterpret_cast<const uint4*>(land1),
+                                                   reinterpret_cast<uint4*>(dst), nbytes / 16, step_word, step);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
@@ -404,6 +525,18 @@ extern "C" int pdnn_ps_wait_next(const uint32_t* flag, uint32_t* step_word, long
 extern "C" int pdnn_delay(long long ns, const uint32_t* guard_closed, const uint32_t* guard_step, void* stream) {
     if (ns <= 0) return 0;
     ps_delay_kernel<<<1, 1, 0, ST(stream)>>>(ns, guard_closed, guard_step);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pdnn_delay_sampled(const pdnn_delay_spec_t* spec, int worker, int layer, const uint32_t* step_word,
+                                  const uint32_t* guard_closed, uint32_t* log_ns, void* stream) {
+    PDNN_REQUIRE(spec != nullptr && step_word != nullptr, "delay_sampled: spec and step word are required");
+    PDNN_REQUIRE(spec->kind >= 0 && spec->kind <= 5, "delay_sampled: unknown kind %d", spec->kind);
+    PDNN_REQUIRE(worker >= 0 && worker < 63 && layer >= 0, "delay_sampled: worker / layer out of range");
+    if (spec->kind == 0) return 0;
+    ps_delay_sampled_kernel<<<1, 1, 0, ST(stream)>>>(*spec, worker, layer, step_word, guard_closed, log_ns);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -210,47 +210,71 @@ int pdnn_ps_push(const float* grad, void* slot_peer, long long n, int slot_is_bf
                  uint32_t step, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
                  void* stream);
 
+#define PDNN_MAX_RECEIVERS 24   /* workers + passive listeners (evaluator ranks) */
+#define PDNN_MAX_BUCKETS 32
+
 typedef struct pdnn_ps_master {
     /* inputs */
-    const void* slots[PDNN_MAX_WORKERS];     /* per-worker gradient slot on the master (bf16 or fp32) */
-    uint32_t* arrival_flags;                 /* [n_workers] written by workers: step number */
-    void* worker_weights[PDNN_MAX_WORKERS];  /* peer pointers: each worker's weight buffer */
-    uint32_t* worker_ready[PDNN_MAX_WORKERS];/* peer pointers: weights_ready word of each worker */
+    const void* slots[PDNN_MAX_WORKERS];     /* per-worker gradient slot on the master (bf16 or fp32), whole model */
+    uint32_t* arrival_flags;                 /* [n_workers][arrival_stride]: word (w, b) = step whose bucket b of worker w landed */
+    int arrival_stride;
+    void* recv_weights[2][PDNN_MAX_RECEIVERS];/* peer pointers: landing buffers; the weights of step s land in [s & 1] */
+    uint32_t* recv_ready[PDNN_MAX_RECEIVERS];/* peer pointers: weights_ready word of each receiver (workers first) */
     uint32_t* worker_closed[PDNN_MAX_WORKERS];/* peer pointers: step_closed word of each worker */
-    void* multicast_weights;                 /* NVLS multicast address of the weight buffers or NULL */
+    void* multicast_weights[2];              /* NVLS multicast address of the landing buffers (per parity) or NULL */
     const void* multicast_slots;             /* NVLS multicast address of the workers' LOCAL gradient slots or NULL: when set
                                                 (and all n are aggregated) the sum is one multimem.ld_reduce in the switch */
     float* master_w;                         /* fp32 master weights */
     float* momentum;                         /* fp32 momentum buffer */
-    uint32_t* control;                       /* >= 64 words of zero-initialised master-local scratch */
+    uint32_t* control;                       /* >= 256 words of zero-initialised master-local scratch */
     long long n;                             /* number of parameters */
     int n_workers;
-    int k;                                   /* aggregate the first k complete gradient sets */
+    int n_receivers;                         /* >= n_workers: every receiver gets the weights and the ready flag */
+    int k;                                   /* aggregate the first k arrivals of every bucket */
     int slot_is_bf16;
     int weights_are_bf16;
     int avg_mode;                            /* 0: 1/k, 1: 1/n (reference python), 2: 1/received */
     float lr, mu;
-    uint32_t step;                           /* step being closed; workers are released with step+1 */
+    uint32_t step;                           /* step being closed; receivers are released with step+1 */
     long long deadline_ns;                   /* >0: interval policy, close with whatever arrived */
     int max_ctas;
     uint32_t* step_ptr;                      /* non-NULL: read `step` from this device word and advance it at the end, so
-                                                that the launch does not depend on the step number (CUDA-graph replay) */
+                                                that the launches do not depend on the step number (CUDA-graph replay) */
     int poison_slots;                        /* debug (race detection): overwrite every gradient slot the master has summed
                                                 with NaN, inside the same kernel and before the workers are released. A
                                                 slot that is ever summed without having been rewritten for its step then
                                                 turns the weights into NaN instead of silently reusing stale data. */
+    int n_buckets;                           /* gradient buckets in arrival order (deepest layers first) */
+    long long bucket_lo[PDNN_MAX_BUCKETS];   /* element range of bucket b: [bucket_lo[b], bucket_hi[b]), multiples of 4 */
+    long long bucket_hi[PDNN_MAX_BUCKETS];
+    long long hard_timeout_ns;               /* a bucket that never sees k arrivals gives up after this long (0 = 30 s) */
+    int poll_sleep_ns;                       /* pause between two looks at the arrival flags (0 = 400 ns) */
 } pdnn_ps_master_t;
 
-/* Master: wait for the first k arrivals of `step`, publish the kill mask to the late workers
- * (step_closed = step in their memory), sum the selected slots in rank order, apply 1/k + momentum SGD
- * to the fp32 master copy, cast and store the new weights into every worker's buffer (unicast peer
- * stores or one multimem store), then release the workers (weights_ready = step+1).
+/* Master, one step = for every bucket b in arrival order {wait kernel, reduce kernel} enqueued on `stream`:
+ * wait for the first k arrivals of bucket b of `step` (one warp polls the per-(worker, bucket) flags), sum the
+ * selected slots in rank order (or in the switch), apply 1/k + momentum SGD to the fp32 master copy, cast and store
+ * the new weights into every receiver's landing buffer of parity (step+1) & 1 (unicast peer stores or one multimem
+ * store). Bucket b is therefore finished while the workers still compute the gradients of bucket b+1. The last
+ * bucket additionally publishes the kill mask to the workers that were not among its first k (step_closed = step in
+ * their memory; the reference kills on the k-th arrival of parameter 0 the same way) and releases every receiver
+ * (weights_ready = step+1).
  * ref: SyncReplicasMaster_NN.train hot loop, pytorch_code/sync_replicas_master_nn.py:117-228
  * (Waitany/aggregate/kill/update/Bcast) and MPI_code/src/distributed/sync_replicas_master_nn.h:46-137.
- * result (device, 8 words): [0]=selected mask, [1]=kill mask, [2]=#received, [3]=step (0xDEAD: the hard timeout
- * expired before k gradient sets arrived), [4]=microseconds waited for the k-th arrival, [5]=microseconds of
- * reduce + update + broadcast (device %globaltimer). */
+ * result (device, 80 words): [0]=selected mask of the last bucket, [1]=kill mask, [2]=#received, [3]=step (0xDEAD:
+ * the hard timeout expired before k arrivals), [4]=microseconds from the start of the step to the k-th arrival of the
+ * last bucket, [5]=microseconds from that arrival to the release (the un-overlapped tail), [6]=gradient sets applied
+ * since the run began, [7]=n_buckets, [8+b]=mask of bucket b, [40+b]=microseconds into the step at which bucket b
+ * had its k arrivals (device %globaltimer). */
 int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* stream);
+/* The {wait, reduce} pair of ONE bucket of that step; pdnn_ps_master_step(args) == for b in 0..n_buckets-1 this call.
+ * Buckets must be enqueued in order on one stream. */
+int pdnn_ps_master_bucket(const pdnn_ps_master_t* args, uint32_t* result, int b, void* stream);
+
+/* Worker: copy this step's landing buffer (land1 when the step is odd) into the private compute copy. The step is
+ * read from *step_word when that is non-NULL (CUDA-graph replay), else taken from `step`. */
+int pdnn_ps_fetch_weights(const void* land0, const void* land1, void* dst, long long nbytes, const uint32_t* step_word,
+                          uint32_t step, void* stream);
 
 /* Worker: block the stream until *ready_flag >= step (ref: distributed_worker.py:202-208 irecv tag 10). */
 int pdnn_ps_wait_flag(const uint32_t* flag, uint32_t value, uint32_t* cur_step_word, long long timeout_ns,
@@ -264,7 +288,27 @@ int pdnn_ps_wait_next(const uint32_t* flag, uint32_t* step_word, long long timeo
 /* Device-side straggler injection: busy-wait `ns` nanoseconds on %globaltimer (aborts early when the
  * guard closes). ref: pure_py_code/distributed_worker.py:130-132 (time.sleep(0.5) per layer). */
 int pdnn_delay(long long ns, const uint32_t* guard_closed, const uint32_t* guard_step, void* stream);
+/* The same injection with the delay SAMPLED on the device: a pure function of (seed, worker, step, layer) through
+ * Philox4x32-10, the step being read from the worker's device-side step word, so the launch does not change from step
+ * to step and replays inside a CUDA graph. Distributions: the reference's constant subset delay and its (commented-out)
+ * uniform 300..1200 ms (distributed_TF/src/distributed_train.py:288-290), plus shifted-exponential / log-normal / Pareto
+ * tails. `log_ns` (nullable) receives the drawn nanoseconds at index `layer`. */
+typedef struct pdnn_delay_spec {
+    int kind;                        /* 0 none, 1 const, 2 uniform, 3 shifted exponential, 4 log-normal, 5 Pareto */
+    float a, b;                      /* const: a = ms | uniform: [a, b] ms | exp: shift a, mean b | lognormal: mu a, sigma b | pareto: xm a, alpha b */
+    float scale;                     /* multiplies the drawn milliseconds */
+    float prob;                      /* probability that a (worker, step, layer) draw delays at all */
+    unsigned long long rank_mask;    /* bit (worker + 1) set: that worker is affected (reference ranks 1..n); 0 = everyone */
+    unsigned long long seed;
+} pdnn_delay_spec_t;
+int pdnn_delay_sampled(const pdnn_delay_spec_t* spec, int worker, int layer, const uint32_t* step_word,
+                       const uint32_t* guard_closed, uint32_t* log_ns, void* stream);
 int pdnn_set_word(uint32_t* p, uint32_t v, void* stream);
+/* Straggler abort guard of the layer kernels (BatchNorm passes, pooling, ReLU / add, im2col / col2im, column sums,
+ * cross-entropy): every such kernel launched by THIS host thread afterwards returns at once when *closed >= *step.
+ * (NULL, NULL) switches it off. GEMM / conv / push entry points take the same pair through their own arguments.
+ * ref: the kill check between backward ops, pytorch_code/model_ops/lenet.py:168-178. */
+int pdnn_set_abort_guard(const uint32_t* closed, const uint32_t* step);
 
 /* Peer-memory plumbing (CUDA IPC): handle is 64 bytes. */
 int pdnn_ipc_get_handle(void* dev_ptr, void* handle_out64);

@@ -57,7 +57,11 @@ def main(argv=None):
     else:
         from .distributed_worker import DistributedWorker
         from .sync_replicas_master_nn import SyncReplicasMaster_NN
-    evaluator_rank = world - 1 if (args.evaluator and backend != "b200" and world >= 3) else None
+    # the last rank evaluates (C++ / TF reference role); on the device backend it is a passive receiver of the broadcast
+    min_world = 2 if (backend == "b200" and args.colocate_worker) else 3
+    evaluator_rank = world - 1 if (args.evaluator and world >= min_world) else None
+    if evaluator_rank is None:
+        args.evaluator = False
     result = None
     if rank == 0:
         master = SyncReplicasMaster_NN(comm=comm, **kwargs_from_args(args, master=True))
@@ -66,8 +70,8 @@ def main(argv=None):
         result = master.train(train_set)
         print("Done sending messages to workers! summary:", result, flush=True)
     elif rank == evaluator_rank:
-        from .evaluator import EvaluatorNN
-        ev = EvaluatorNN(comm, val_set, **kwargs_from_args(args, master=False))
+        from .evaluator import B200EvaluatorNN, EvaluatorNN
+        ev = (B200EvaluatorNN if backend == "b200" else EvaluatorNN)(comm, val_set, **kwargs_from_args(args, master=False))
         ev.build_model()
         result = ev.train()
     else:

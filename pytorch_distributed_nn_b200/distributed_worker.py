@@ -68,11 +68,11 @@ class DistributedWorker(NN_Trainer):
     def build_model(self):
         if self.comm.backend == "b200":
             from .parallel.b200_ps import B200ParameterServer
-            from .parallel.delays import parse_delay_spec
-            delay_fn = parse_delay_spec(self.inject_delay) if self.inject_delay else None
+            from .parallel.delays import DeviceDelay
             kw = self.kwargs
+            device_delay = DeviceDelay(self.inject_delay, seed=int(kw.get("seed", 1) or 1)) if self.inject_delay else None
             policy = kw.get("straggler_policy", "kofn" if self._kill_aware else "all")
-            n_workers = self.world_size if self.colocate else self.world_size - 1
+            n_workers = (self.world_size if self.colocate else self.world_size - 1) - (1 if self.has_evaluator else 0)
             k = kw.get("kill_threshold")
             if policy == "all" or not k:
                 k = n_workers
@@ -81,8 +81,8 @@ class DistributedWorker(NN_Trainer):
                                           momentum=self.momentum, num_aggregate=max(1, min(int(k), n_workers)), avg_mode=kw.get("avg_mode", "k"),
                                           grad_dtype="bf16" if self.grad_dtype == "bf16" else "fp32", colocate=self.colocate,
                                           n_buckets=self.n_buckets, seed=int(kw.get("seed", 1) or 1),
-                                          deadline_ms=interval_ms if policy == "interval" else 0.0, delay_fn=delay_fn,
-                                          group=self.comm.group, device=self.comm.device)
+                                          deadline_ms=interval_ms if policy == "interval" else 0.0, device_delay=device_delay,
+                                          group=self.comm.group, device=self.comm.device, n_listeners=1 if self.has_evaluator else 0)
             self.network = self.ps.net
             return self
         from .models import build_model
@@ -171,18 +171,21 @@ class DistributedWorker(NN_Trainer):
         self.comm.wait_all([self.comm.send_grad_eos()])
 
     def _train_b200(self, train_loader):
+        """Same loop as the master's colocated worker: ``B200ParameterServer.fit`` (pinned staging + CUDA-graph replay)."""
         ps = self.ps
-        dev = ps.device
         steps = self.max_steps or 20000
-        for i in range(ps.step, steps + 1):
-            x, y = train_loader.next_batch(self.batch_size)
-            loss = ps.worker_step(x.to(dev, non_blocking=True).float(), y.to(dev, non_blocking=True))
-            ps.step += 1
-            if i % self.log_interval == 0 or i == 1 or i == steps:
-                lv = float(loss)          # synchronises: bounds how far the host runs ahead of the device
-                self.history.append({"step": i, "loss": lv})
-                print("Worker: {}, Cur Step: {}, Train Loss: {:.4f}".format(self.rank, i, lv), flush=True)
-        torch.cuda.synchronize()
+
+        def on_log(i, loss):
+            self.history.append({"step": i, "loss": loss})
+            print("Worker: {}, Cur Step: {}, Train Loss: {:.4f}".format(self.rank, i, loss), flush=True)
+
+        eval_freq = int(self.kwargs.get("eval_freq", 0) or 0)
+
+        def should_log(i):     # the same predicate as the master's: every rank synchronises with its device at the same steps
+            return i % self.log_interval == 0 or (eval_freq and i % eval_freq == 0)
+
+        ps.fit(train_loader, steps, log_interval=self.log_interval, on_log=on_log, should_log=should_log,
+               cuda_graph=bool(self.kwargs.get("cuda_graph", True)))
         return self.history
 
     # ---- message-backend pieces (reference method names) -------------------------------------------------------

@@ -48,6 +48,7 @@ class Network:
         self.w32 = self.w = self.g = None
         self.buckets: List[Bucket] = []
         self.on_bucket: Optional[Callable[[Bucket], None]] = None
+        self.layer_hook: Optional[Callable[[int], None]] = None   # called before every backward layer (straggler injection)
         self._scratch = None
         self._param_bucket = {}
         self.loss = torch.zeros(1, device=self.device, dtype=F32)
@@ -295,7 +296,9 @@ class Network:
 
     def backward(self):
         dy = self.dlogits
-        for layer in reversed(self.layers):
+        for idx, layer in enumerate(reversed(self.layers)):
+            if self.layer_hook is not None:     # the reference sleeps before every backward layer (pure_py_code/distributed_worker.py:130-132)
+                self.layer_hook(idx)
             dy = layer.backward(dy)
         self.pool_fresh = False
 
@@ -325,6 +328,7 @@ class FlatParams:
         self.g = torch.zeros(self.total, device=dev, dtype=F32)
         self.loss = torch.zeros(1, device=dev, dtype=F32)
         self.on_bucket = None
+        self.layer_hook = None
         n_buckets = max(1, n_buckets)
         step = (self.total // n_buckets + ALIGN - 1) // ALIGN * ALIGN
         self.buckets, end = [], self.total

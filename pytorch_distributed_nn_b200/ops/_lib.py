@@ -29,18 +29,30 @@ class Epilogue(C.Structure):
     ]
 
 
+MAX_RECEIVERS = 24
+MAX_BUCKETS = 32
+
+
 class PSMaster(C.Structure):
     """Mirror of pdnn_ps_master_t."""
     _fields_ = [
-        ("slots", C.c_void_p * MAX_WORKERS), ("arrival_flags", C.c_void_p),
-        ("worker_weights", C.c_void_p * MAX_WORKERS), ("worker_ready", C.c_void_p * MAX_WORKERS),
-        ("worker_closed", C.c_void_p * MAX_WORKERS), ("multicast_weights", C.c_void_p), ("multicast_slots", C.c_void_p),
+        ("slots", C.c_void_p * MAX_WORKERS), ("arrival_flags", C.c_void_p), ("arrival_stride", C.c_int),
+        ("recv_weights", (C.c_void_p * MAX_RECEIVERS) * 2), ("recv_ready", C.c_void_p * MAX_RECEIVERS),
+        ("worker_closed", C.c_void_p * MAX_WORKERS), ("multicast_weights", C.c_void_p * 2), ("multicast_slots", C.c_void_p),
         ("master_w", C.c_void_p), ("momentum", C.c_void_p), ("control", C.c_void_p),
-        ("n", C.c_longlong), ("n_workers", C.c_int), ("k", C.c_int), ("slot_is_bf16", C.c_int),
+        ("n", C.c_longlong), ("n_workers", C.c_int), ("n_receivers", C.c_int), ("k", C.c_int), ("slot_is_bf16", C.c_int),
         ("weights_are_bf16", C.c_int), ("avg_mode", C.c_int), ("lr", C.c_float), ("mu", C.c_float),
         ("step", C.c_uint32), ("deadline_ns", C.c_longlong), ("max_ctas", C.c_int), ("step_ptr", C.c_void_p),
-        ("poison_slots", C.c_int),
+        ("poison_slots", C.c_int), ("n_buckets", C.c_int),
+        ("bucket_lo", C.c_longlong * MAX_BUCKETS), ("bucket_hi", C.c_longlong * MAX_BUCKETS), ("hard_timeout_ns", C.c_longlong),
+        ("poll_sleep_ns", C.c_int),
     ]
+
+
+class DelaySpec(C.Structure):
+    """Mirror of pdnn_delay_spec_t."""
+    _fields_ = [("kind", C.c_int), ("a", C.c_float), ("b", C.c_float), ("scale", C.c_float), ("prob", C.c_float),
+                ("rank_mask", C.c_ulonglong), ("seed", C.c_ulonglong)]
 
 
 class FcPsConfig(C.Structure):
@@ -133,9 +145,13 @@ _SIGS = {
     "pdnn_ps_push_dev": [_P, _P, _L, _I, _P, _P, _P, _P, _I, _P],
     "pdnn_ps_wait_next": [_P, _P, _L, _P],
     "pdnn_ps_master_step": [C.POINTER(PSMaster), _P, _P],
+    "pdnn_ps_master_bucket": [C.POINTER(PSMaster), _P, _I, _P],
+    "pdnn_ps_fetch_weights": [_P, _P, _P, _L, _P, _U, _P],
     "pdnn_ps_wait_flag": [_P, _U, _P, _L, _P],
     "pdnn_delay": [_L, _P, _P, _P],
+    "pdnn_delay_sampled": [C.POINTER(DelaySpec), _I, _I, _P, _P, _P, _P],
     "pdnn_set_word": [_P, _U, _P],
+    "pdnn_set_abort_guard": [_P, _P],
     "pdnn_p2p_copy": [_P, _P, _L, _I, _P],
     "pdnn_malloc": [C.POINTER(C.c_void_p), _L],
     "pdnn_free": [_P],

@@ -25,8 +25,10 @@ _GUARD = [None, None]
 
 
 def set_abort_guard(closed_word, step_word) -> None:
-    """Every guarded kernel launched afterwards returns immediately once *closed >= *step."""
+    """Every guarded kernel launched afterwards returns immediately once *closed >= *step (GEMM / conv kernels through
+    their epilogue arguments, the layer kernels of nn_kernels.cu through the library's per-thread guard)."""
     _GUARD[0], _GUARD[1] = closed_word, step_word
+    call("pdnn_set_abort_guard", ptr(closed_word), ptr(step_word))
 
 
 def _epi(out, ldo, out_mode, relu=False, alpha=1.0, bias=None, residual=None, max_ctas=0):

@@ -100,6 +100,7 @@ class SyncReplicasMaster_NN(NN_Trainer):
         self.n_buckets = int(kwargs.get("n_buckets", 8) or 8)
         self.seed = int(kwargs.get("seed", 1) or 1)
         self.inject_delay = kwargs.get("inject_delay", "")
+        self.cuda_graph = bool(kwargs.get("cuda_graph", True))
         self.logger = JsonlLogger(self.train_dir or None, comm.Get_rank(), "master")
         self.timeline = Timeline((self.train_dir + "/timeline_master") if self.train_dir else None)
         self.step_log = []          # (step, selected workers, killed workers, gather seconds)
@@ -133,8 +134,8 @@ class SyncReplicasMaster_NN(NN_Trainer):
 
     def _build_b200(self):
         from .parallel.b200_ps import B200ParameterServer
-        from .parallel.delays import parse_delay_spec
-        delay_fn = parse_delay_spec(self.inject_delay) if self.inject_delay else None
+        from .parallel.delays import DeviceDelay
+        device_delay = DeviceDelay(self.inject_delay, seed=self.seed) if self.inject_delay else None
         init_sd, init_mom, self.step_offset = None, None, 0
         if self.resume:
             # the device protocol always counts from 1; the global step (checkpoint names) continues from the file
@@ -143,8 +144,9 @@ class SyncReplicasMaster_NN(NN_Trainer):
                                       momentum=self.momentum, num_aggregate=self._should_kill_threshold, avg_mode=self.avg_mode,
                                       grad_dtype="bf16" if self.grad_dtype == "bf16" else "fp32", colocate=self.colocate or self.world_size == 1,
                                       n_buckets=self.n_buckets, seed=self.seed,
-                                      deadline_ms=self.interval_ms if self.policy == "interval" else 0.0, delay_fn=delay_fn,
-                                      group=self.comm.group, device=self.comm.device, init_state_dict=init_sd, init_momentum=init_mom)
+                                      deadline_ms=self.interval_ms if self.policy == "interval" else 0.0, device_delay=device_delay,
+                                      group=self.comm.group, device=self.comm.device, init_state_dict=init_sd, init_momentum=init_mom,
+                                      n_listeners=1 if self.has_evaluator else 0)
         self.network = self.ps.net
         return self
 
@@ -222,33 +224,33 @@ class SyncReplicasMaster_NN(NN_Trainer):
 
     # ---- b200 path ---------------------------------------------------------------------------------------
     def _train_b200(self, train_loader):
+        """The device backend's loop is ``B200ParameterServer.fit`` (pinned double-buffered input staging, the whole step
+        replayed from a CUDA graph after two eager steps); this role logs, checkpoints and keeps the step records."""
         ps = self.ps
         timer = StepTimer(self.batch_size * ps.k)
-        dev = ps.device
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-        t_prev = None
-        for i in range(ps.step, self.max_steps + 1):
-            ev[0].record()
-            if ps.is_worker:
-                x, y = train_loader.next_batch(self.batch_size)
-                ps.worker_step(x.to(dev, non_blocking=True).float(), y.to(dev, non_blocking=True))
-            ps.master_step()
-            ps.step += 1
-            ev[1].record()
-            if i % self.log_interval == 0 or i == 1 or (self.eval_freq and i % self.eval_freq == 0) or i == self.max_steps:
-                ev[1].synchronize()
-                sel, kill, nrecv, st = ps.last_result()
-                ms = ev[0].elapsed_time(ev[1])
-                timer.add(ms)
-                selected = [w for w in range(ps.n_workers) if sel >> w & 1]
-                killed = [w for w in range(ps.n_workers) if kill >> w & 1]
-                self.step_log.append((i, selected, killed, ms / 1e3))
-                print("Master Step: {} selected: {} killed: {} Step Time: {:.6f}".format(i, selected, killed, ms / 1e3), flush=True)
-                self.logger.log(step=i, selected=selected, killed=killed, step_ms=ms)
-                if self.eval_freq and self.train_dir and i % self.eval_freq == 0:
-                    self.cur_step = i + getattr(self, "step_offset", 0)
-                    self.save_checkpoint()
-        torch.cuda.synchronize()
+        mark = {"t": time.perf_counter(), "step": ps.step - 1}
+
+        def on_log(i, loss):
+            sel, kill, nrecv, st = ps.last_result()
+            now = time.perf_counter()
+            ms = (now - mark["t"]) * 1e3 / max(1, i - mark["step"])        # mean step time since the previous log line
+            mark["t"], mark["step"] = now, i
+            timer.add(ms)
+            selected = [w for w in range(ps.n_workers) if sel >> w & 1]
+            killed = [w for w in range(ps.n_workers) if kill >> w & 1]
+            self.step_log.append((i, selected, killed, ms / 1e3))
+            print("Master Step: {} selected: {} killed: {} Step Time: {:.6f}".format(i, selected, killed, ms / 1e3), flush=True)
+            self.logger.log(step=i, selected=selected, killed=killed, step_ms=ms, loss=loss, device_timeline_us=ps.last_timing_us)
+            if self.eval_freq and self.train_dir and i % self.eval_freq == 0:
+                self.cur_step = i + getattr(self, "step_offset", 0)
+                self.save_checkpoint()
+                mark["t"] = time.perf_counter()
+
+        def should_log(i):
+            return i % self.log_interval == 0 or (self.eval_freq and i % self.eval_freq == 0)
+
+        ps.fit(train_loader if ps.is_worker else None, self.max_steps, log_interval=self.log_interval, on_log=on_log,
+               should_log=should_log, cuda_graph=self.cuda_graph)
         if self._pending_ckpt is not None:
             self._pending_ckpt.join()
         self.cur_step = ps.step

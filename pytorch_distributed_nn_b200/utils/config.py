@@ -41,6 +41,8 @@ def add_fit_args(parser: argparse.ArgumentParser, distributed: bool = True) -> a
         a.add_argument("--colocate-worker", action="store_true", default=False, help="GPU 0 hosts master AND a worker (b200 backend)")
         a.add_argument("--evaluator", action="store_true", default=False, help="dedicate the last rank to evaluation (C++/TF reference role)")
         a.add_argument("--n-buckets", type=int, default=8, help="gradient buckets per step (b200 backend)")
+        a.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false", default=True,
+                       help="b200 backend: enqueue every kernel of every step from the host instead of replaying a CUDA graph")
     return parser
 
 
@@ -54,7 +56,7 @@ def kwargs_from_args(args, master: bool):
     # data path (NVLS gather vs. pushed slots) from k and the deadline, so workers receive them too
     kw["kill_threshold"] = getattr(args, "num_aggregate", None)
     for extra in ("max_steps", "train_dir", "eval_freq", "resume", "straggler_policy", "interval_ms", "avg_mode", "inject_delay",
-                  "grad_dtype", "colocate_worker", "n_buckets", "log_interval", "seed", "evaluator"):
+                  "grad_dtype", "colocate_worker", "n_buckets", "log_interval", "seed", "evaluator", "cuda_graph", "test_batch_size"):
         if hasattr(args, extra):
             kw[extra] = getattr(args, extra)
     return kw

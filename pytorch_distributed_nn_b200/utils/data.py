@@ -224,7 +224,7 @@ class PinnedBatchStager:
     def stage(self, x, y):
         b = self.i % len(self.hx)
         self.i += 1
-        self.hx[b].copy_(x)
+        self.hx[b].view(-1).copy_(x.reshape(-1))          # same element count, any host layout ([B,1,28,28] for a [B,784] net)
         self.hy[b].copy_(y)
         with torch.cuda.stream(self.stream):
             if self.used[b]:

@@ -90,25 +90,27 @@ def test_ps_single_worker_update_equals_momentum_sgd():
         m = 0.9 * m + g
         w = w - 0.1 * m
         assert torch.allclose(net.w32, w, rtol=1e-5, atol=1e-6)
-        assert torch.equal(net.w[: net.total], net.w32)      # fp32 network: broadcast copy == master copy
+        # fp32 network: the broadcast copy (landing buffer of the NEXT step's parity) == master copy
+        assert torch.equal(ps.land[ps.step & 1][: net.total], net.w32)
     ps.close()
 
 
-def _master_args(n_workers, n, k, slots, flags, weights, ready, closed, master_w, mom, ctl, step, avg_mode=0, bf16_slots=False,
-                 lr=0.1, mu=0.5):
+def _master_args(n_workers, n, k, slots, flags, stride, land, ready, closed, master_w, mom, ctl, step, buckets, avg_mode=0,
+                 bf16_slots=False, lr=0.1, mu=0.5):
     from pytorch_distributed_nn_b200.ops import _lib
     m = _lib.PSMaster()
     for w in range(n_workers):
         m.slots[w] = slots[w].data_ptr()
-        m.worker_weights[w] = weights[w].data_ptr()
-        m.worker_ready[w] = ready.data_ptr() + 4 * w
+        for par in range(2):
+            m.recv_weights[par][w] = land[par][w].data_ptr()
+        m.recv_ready[w] = ready.data_ptr() + 4 * w
         m.worker_closed[w] = closed.data_ptr() + 4 * w
     m.arrival_flags = flags.data_ptr()
-    m.multicast_weights = None
+    m.arrival_stride = stride
     m.master_w = master_w.data_ptr()
     m.momentum = mom.data_ptr()
     m.control = ctl.data_ptr()
-    m.n, m.n_workers, m.k = n, n_workers, k
+    m.n, m.n_workers, m.n_receivers, m.k = n, n_workers, n_workers, k
     m.slot_is_bf16 = int(bf16_slots)
     m.weights_are_bf16 = 1
     m.avg_mode = avg_mode
@@ -116,42 +118,87 @@ def _master_args(n_workers, n, k, slots, flags, weights, ready, closed, master_w
     m.step = step
     m.deadline_ns = 0
     m.max_ctas = 0
+    m.n_buckets = len(buckets)
+    for b, (lo, hi) in enumerate(buckets):
+        m.bucket_lo[b], m.bucket_hi[b] = lo, hi
     return m
 
 
 @pytest.mark.parametrize("avg_mode", ["k", "n"])
 def test_master_kernel_k_of_n_matches_oracle(avg_mode):
-    """All ranks' data on one GPU (the multi-rank path is emulated as ONE kernel over every worker's slot):
-    workers 0, 2, 3 of 4 have arrived for step 7, worker 1 carries a stale flag; k = 3."""
+    """All ranks' data on one GPU (the multi-rank path is emulated over every worker's slot), two buckets, k = 3 of 4,
+    step 7: bucket 0 (arrives first, the deep half of the model) has workers 0, 2, 3, bucket 1 has workers 0, 1, 3.
+    Each bucket is averaged over ITS first k arrivals (reference: per-layer accumulation in arrival order,
+    sync_replicas_master_nn.py:148-166); the kill set is who missed the last bucket (:172-187)."""
     from pytorch_distributed_nn_b200.ops import _lib
     from pytorch_distributed_nn_b200.parallel.oracle import kofn_update
     from pytorch_distributed_nn_b200.parallel.protocol import AVG_MODES
-    n, nw, k, step = 100_003 // 4 * 4, 4, 3, 7
+    n, nw, k, step, stride = 100_000, 4, 3, 7, 8
+    buckets = [(60_000, 100_000), (0, 60_000)]
     dev = "cuda"
     grads = [torch.randn(n, device=dev) for _ in range(nw)]
-    flags = torch.tensor([7, 6, 7, 7], device=dev, dtype=torch.int32)
-    weights = [torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(nw)]
+    flags = torch.zeros(nw, stride, device=dev, dtype=torch.int32)
+    flags[:, 0] = torch.tensor([7, 6, 7, 7])
+    flags[:, 1] = torch.tensor([7, 7, 3, 7])
+    land = [[torch.zeros(n, device=dev, dtype=torch.bfloat16) for _ in range(nw)] for _ in range(2)]
     ready = torch.zeros(nw, device=dev, dtype=torch.int32)
     closed = torch.zeros(nw, device=dev, dtype=torch.int32)
     w0 = torch.randn(n, device=dev)
     m0 = torch.randn(n, device=dev) * 0.1
     master_w, mom = w0.clone(), m0.clone()
-    ctl = torch.zeros(64, device=dev, dtype=torch.int32)
-    result = torch.zeros(8, device=dev, dtype=torch.int32)
-    args = _master_args(nw, n, k, grads, flags, weights, ready, closed, master_w, mom, ctl, step, AVG_MODES[avg_mode])
+    ctl = torch.zeros(256, device=dev, dtype=torch.int32)
+    result = torch.zeros(80, device=dev, dtype=torch.int32)
+    args = _master_args(nw, n, k, grads, flags, stride, land, ready, closed, master_w, mom, ctl, step, buckets, AVG_MODES[avg_mode])
     _lib.call("pdnn_ps_master_step", C.byref(args), result.data_ptr(), _lib.stream_ptr())
     torch.cuda.synchronize()
-    sel, kill, nrecv, st = [int(v) for v in result.tolist()[:4]]
-    assert (sel, kill, nrecv, st) == (0b1101, 0b0010, 3, 7)
-    assert closed.tolist() == [0, 7, 0, 0]                 # only the straggler is told to abandon step 7
+    r = [int(v) for v in result.tolist()]
+    assert tuple(r[:4]) == (0b1011, 0b0100, 3, 7) and r[7] == 2 and r[8:10] == [0b1101, 0b1011] and r[6] == 3
+    assert closed.tolist() == [0, 0, 7, 0]                 # only the worker that missed the last bucket abandons step 7
     assert ready.tolist() == [8, 8, 8, 8]                  # everybody is released into step 8
-    w_ref, m_ref, selected, killed = kofn_update(w0.cpu(), m0.cpu(), {i: g.cpu() for i, g in enumerate(grads)}, [0, 2, 3], k, nw,
-                                                 lr=0.1, mu=0.5, avg_mode=avg_mode)
-    assert selected == [0, 2, 3] and killed == [1]
-    assert torch.allclose(master_w.cpu(), w_ref, rtol=1e-5, atol=1e-6)
-    assert torch.allclose(mom.cpu(), m_ref, rtol=1e-5, atol=1e-6)
-    for w in weights:
-        assert torch.equal(w, master_w.bfloat16())
+    for (lo, hi), who in zip(buckets, ([0, 2, 3], [0, 1, 3])):
+        w_ref, m_ref, selected, _ = kofn_update(w0[lo:hi].cpu(), m0[lo:hi].cpu(), {i: g[lo:hi].cpu() for i, g in enumerate(grads)}, who, k, nw,
+                                                lr=0.1, mu=0.5, avg_mode=avg_mode)
+        assert selected == who
+        assert torch.allclose(master_w[lo:hi].cpu(), w_ref, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(mom[lo:hi].cpu(), m_ref, rtol=1e-5, atol=1e-6)
+    for w in range(nw):
+        assert torch.equal(land[0][w], master_w.bfloat16())        # weights of step 8 land in parity 0
+        assert float(land[1][w].float().abs().max()) == 0.0        # the buffer step 7 is still being read from is untouched
+    # a second step through the same control block (counters were reset): step 8, everybody present
+    flags[:] = 8
+    args.step = 8
+    _lib.call("pdnn_ps_master_step", C.byref(args), result.data_ptr(), _lib.stream_ptr())
+    torch.cuda.synchronize()
+    r = [int(v) for v in result.tolist()]
+    assert tuple(r[:4]) == (0b0111, 0b1000, 3, 8) and r[6] == 6 and ready.tolist() == [9, 9, 9, 9]
+    assert torch.equal(land[1][0], master_w.bfloat16())
+
+
+def test_push_abort_in_mid_grid_keeps_the_handshake_consistent():
+    """A kill can land while a push grid is running: some CTAs copy, some abort. The completion counter must come back to
+    zero and the arrival flag must stay down for that launch -- and the next, un-aborted push must publish normally."""
+    from pytorch_distributed_nn_b200.ops import _lib
+    n = 4_000_000
+    g = torch.randn(n, device="cuda")
+    slot = torch.zeros(n, device="cuda", dtype=torch.bfloat16)
+    flag = torch.zeros(1, device="cuda", dtype=torch.int32)
+    stepw = torch.tensor([5], device="cuda", dtype=torch.int32)
+    for trial in range(20):
+        closed = torch.tensor([4], device="cuda", dtype=torch.int32)
+        side = torch.cuda.Stream()
+        _lib.call("pdnn_ps_push", g, slot, n, 1, flag, 5, closed, stepw, 8, _lib.stream_ptr())      # 8 CTAs: a long grid
+        with torch.cuda.stream(side):
+            closed.fill_(5)                                                                          # the kill, racing with the grid
+        torch.cuda.synchronize()
+        flag_after_race = int(flag)
+        assert flag_after_race in (0, 5)
+        flag.zero_()
+        closed.fill_(4)
+        torch.cuda.synchronize()
+        _lib.call("pdnn_ps_push", g, slot, n, 1, flag, 5, closed, stepw, 8, _lib.stream_ptr())
+        torch.cuda.synchronize()
+        assert int(flag) == 5 and torch.equal(slot, g.bfloat16()), trial     # a stuck counter would publish early or never
+        flag.zero_()
 
 
 def test_push_kernel_casts_and_flags():
