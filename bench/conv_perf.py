@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Isolated timings of the implicit-GEMM conv kernels on the ResNet / VGG stage shapes (batch 1024) and of one big GEMM.
 
-    python bench/conv_perf.py            # PDNN_CLUSTER=1 two-CTA multicast schedule, =2 CTA pair (cta_group::2)
+    python bench/conv_perf.py            # PDNN_CLUSTER=2 CTA pair (cta_group::2)
 """
 import os
 import sys
@@ -28,7 +28,7 @@ def time_ms(fn, iters=20):
 
 def main():
     torch.cuda.set_device(0)
-    tag = {"1": "multicast", "2": "pair"}.get(os.environ.get("PDNN_CLUSTER", ""), "single")
+    tag = {"2": "pair"}.get(os.environ.get("PDNN_CLUSTER", ""), "single")
     for (n, h, c, k) in [(1024, 16, 128, 128), (1024, 8, 256, 256), (1024, 4, 512, 512), (1024, 16, 256, 256), (1024, 8, 512, 512)]:
         x = torch.randn(n, h, h, c, device="cuda").bfloat16()
         w = (torch.randn(k, 3, 3, c, device="cuda") / (3 * c ** 0.5)).bfloat16()

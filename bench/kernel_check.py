@@ -205,12 +205,6 @@ def _cluster_cases(mode, tag):
 
 
 @case
-def gemm_cluster():
-    """The two-CTA cluster schedule (TMA multicast of B, multicast stage release) against the fp32 reference."""
-    return _cluster_cases(1, "cluster")
-
-
-@case
 def gemm_pair():
     """The CTA-pair schedule (cta_group::2, M = 256 MMAs over both CTAs' shared memory) against the fp32 reference."""
     return _cluster_cases(2, "pair")

@@ -160,16 +160,6 @@ __device__ __forceinline__ void st_shared_remote_u32(uint32_t local_saddr, uint3
         ::"r"(local_saddr), "r"(cta_rank), "r"(v)
         : "memory");
 }
-// TMA tile load delivered to the same shared-memory offset of every CTA in cta_mask; each destination CTA's mbarrier
-// (same offset) receives the complete_tx for the bytes that landed in that CTA.
-__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
-                                                      uint16_t cta_mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "h"(cta_mask)
-        : "memory");
-}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c0,
                                             int c1, int c2, int c3) {
     asm volatile(
@@ -301,8 +291,7 @@ __device__ __forceinline__ void umma_commit_pred(uint32_t bar, uint32_t issue) {
         ::"r"(bar), "r"(issue)
         : "memory");
 }
-// the same arrival delivered to the mbarrier at this offset in every CTA of cta_mask (stage release in a cluster whose
-// CTAs fill each other's stages by multicast)
+// the same arrival delivered to the mbarrier at this offset in every CTA of cta_mask
 __device__ __forceinline__ void umma_commit_multicast_pred(uint32_t bar, uint16_t cta_mask, uint32_t issue) {
     asm volatile(
         "{\n\t.reg .pred q;\n\t"

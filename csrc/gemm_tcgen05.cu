@@ -71,10 +71,7 @@ struct SmemLayout {
     static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
 };
 
-// CL == 2: launched as clusters of two CTAs that work on two M-tiles of the same N-tile at the same time; each CTA fetches
-// half of every B (filter / weight) tile and TMA-multicasts it into both, so the L2 -> SMEM traffic for B is halved
-// (these kernels are bound by that feed, not by the tensor pipe). K-major B only, no split-K.
-// CL == 3: the same pairing as a CTA PAIR (cta_group::2). Each CTA loads its own A tile and only ITS half of the B tile;
+// CL == 3: clusters of two CTAs that work on two M-tiles of the same N-tile as a CTA PAIR (cta_group::2). Each CTA loads its own A tile and only ITS half of the B tile;
 // the leader (cluster rank 0) issues M = 256 MMAs that read both CTAs' shared memory and write each CTA's own TMEM. Every
 // SM then ingests 16 KB + B/2 per k-block instead of 16 KB + B: ncu shows these kernels bound by that ingest (tensor pipe
 // 51 % active on the stage-3 conv), which multicast cannot change because it still delivers all of B to every SM.
@@ -128,7 +125,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), CL == 2 ? 2 : 1);   // multicast pair: a stage is free once BOTH CTAs consumed it
+            mbar_init(empty_bar(s), 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull_bar(a), 1);
@@ -219,9 +216,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         }
                         if (pair_ld)     // my half of the rows, into my own stage (the pair MMA reads both halves in place)
                             tma_load_2d_2cta(sb, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2));
-                        else if (CL == 2)     // my half of the rows, into both CTAs
-                            tma_load_2d_multicast(sb + cta_rank * (BN / 2) * 128, &tmB, fb, kcol, nt * BN + (int)cta_rank * (BN / 2),
-                                                  (uint16_t)0x3);
                         else
                             tma_load_2d(sb, &tmB, fb, kcol, nt * BN);
                     } else if (BMODE == OP_MN2D) {
@@ -295,8 +289,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         umma_commit_2cta_multicast_pred(empty_bar(stage), (uint16_t)0x3, issue);
                         if (kit == k_end - 1) umma_commit_2cta_multicast_pred(tfull_bar(acc), (uint16_t)0x3, issue);
                     } else {
-                        if (CL == 2) umma_commit_multicast_pred(empty_bar(stage), (uint16_t)0x3, issue);
-                        else umma_commit_pred(empty_bar(stage), issue);
+                        umma_commit_pred(empty_bar(stage), issue);
                         if (kit == k_end - 1) umma_commit_pred(tfull_bar(acc), issue);
                     }
                 }
@@ -580,14 +573,15 @@ static int launch_gemm_cluster(const CUtensorMap& tmA, const CUtensorMap& tmB, c
     PDNN_COUNT_LAUNCH();
     return 0;
 }
-// Opt-in (PDNN_CLUSTER=1): measured on B200 the multicast schedule is numerically identical and exactly as fast as
-// the single-CTA one (conv 3x3 n1024 8x8 c256 k256: 72.6 us vs 72.3 us; 16x16 c128 k128: 120.4 vs 118.4 us) -- these
-// shapes are bound by the tensor pipe / wave quantisation (512 tiles on 148 CTAs), not by the B feed from L2.
-static int g_cluster_mode = -1;   // -1: not read yet; 0 off, 1 multicast pair (CL = 2), 2 CTA pair / cta_group::2 (CL = 3)
+// Opt-in (PDNN_CLUSTER=2): the CTA-pair schedule. A two-CTA schedule that TMA-multicast the B tile into both CTAs was
+// measured exactly as fast as the single-CTA one (conv 3x3 n1024 8x8 c256 k256: 72.6 us vs 72.3 us) and has been removed:
+// the operand pointers of this entry point are the caller's, and TMA multicast loads here read only this GPU's memory,
+// since on B200 a TMA multicast load from another GPU's memory hung the GPU. Every TMA load of this library is unicast.
+static int g_cluster_mode = -1;   // -1: not read yet; 0 off, 2 CTA pair / cta_group::2 (CL = 3)
 static int want_cluster(int bn, const GemmParams& p) {
     if (g_cluster_mode < 0) {
         const char* e = getenv("PDNN_CLUSTER");
-        g_cluster_mode = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+        g_cluster_mode = (e != nullptr && e[0] == '2') ? 2 : 0;
     }
     const bool ok = bn >= 128 && p.k_splits == 1 && (p.m_tiles % 2) == 0 && p.m_tiles * p.n_tiles >= 4 && p.out_remap == 0;
     return ok ? g_cluster_mode : 0;
@@ -595,12 +589,9 @@ static int want_cluster(int bn, const GemmParams& p) {
 template <int AMODE, int BMODE>
 static int dispatch_cluster(int mode, int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
                             cudaStream_t stream) {
-    if (mode == 2) {
-        if (bn == 128) return launch_gemm_cluster<AMODE, BMODE, 128, 3>(tmA, tmB, p, max_ctas, stream);
-        return launch_gemm_cluster<AMODE, BMODE, 256, 3>(tmA, tmB, p, max_ctas, stream);
-    }
-    if (bn == 128) return launch_gemm_cluster<AMODE, BMODE, 128, 2>(tmA, tmB, p, max_ctas, stream);
-    return launch_gemm_cluster<AMODE, BMODE, 256, 2>(tmA, tmB, p, max_ctas, stream);
+    (void)mode;      // the CTA pair is the only cluster schedule
+    if (bn == 128) return launch_gemm_cluster<AMODE, BMODE, 128, 3>(tmA, tmB, p, max_ctas, stream);
+    return launch_gemm_cluster<AMODE, BMODE, 256, 3>(tmA, tmB, p, max_ctas, stream);
 }
 
 template <int AMODE, int BMODE>
@@ -654,7 +645,7 @@ using namespace pdnn;
 
 extern "C" int pdnn_set_cluster_mode(int on) {
     const int prev = pdnn::g_cluster_mode;
-    pdnn::g_cluster_mode = (on == 1 || on == 2) ? on : 0;
+    pdnn::g_cluster_mode = on == 2 ? 2 : 0;
     return prev < 0 ? 0 : prev;
 }
 

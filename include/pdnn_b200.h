@@ -63,9 +63,9 @@ int pdnn_conv_stem_supported(int batch, int H, int W, int C, int Kout, int R, in
 int pdnn_conv_stem_bf16(const void* x, const void* w_pad, int batch, int H, int W, int C, int Kout,
                         const pdnn_epilogue_t* epi, void* col, float* bn_stats, void* stream);
 
-/* Two-CTA cluster schedules of the K-major GEMM / conv fprop kernels. 0 = off (default), 1 = each CTA multicasts half of
- * every B tile into both, 2 = CTA pair (cta_group::2: the leader issues M = 256 MMAs over both CTAs' shared memory, every
- * CTA loads only its half of B). Env PDNN_CLUSTER=1|2 sets it at first use. Returns the previous setting. */
+/* Two-CTA cluster schedule of the K-major GEMM / conv fprop kernels. 0 = off (default), 2 = CTA pair (cta_group::2: the
+ * leader issues M = 256 MMAs over both CTAs' shared memory, every CTA loads only its half of B with unicast TMA loads).
+ * Any other value means off. Env PDNN_CLUSTER=2 sets it at first use. Returns the previous setting. */
 int pdnn_set_cluster_mode(int on);
 
 int pdnn_conv_fprop_bf16(const void* x, const void* wgt, int batch, int H, int W, int C, int Kout,
