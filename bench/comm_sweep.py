@@ -54,6 +54,8 @@ def main():
     ap.add_argument("--max-mb", type=int, default=1024)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--out", default="")
+    ap.add_argument("--no-cuda-graph", action="store_true")
+    ap.add_argument("--n-buckets", type=int, default=1)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -66,9 +68,22 @@ def main():
     size = 1024
     while size <= args.max_mb * (1 << 20):
         n = size // 2                                   # bf16 parameters
-        ps = B200ParameterServer(f"Flat{n}", 1, rank, world, lr=0.01, momentum=0.5, grad_dtype="bf16", colocate=True, n_buckets=1)
+        ps = B200ParameterServer(f"Flat{n}", 1, rank, world, lr=0.01, momentum=0.5, grad_dtype="bf16", colocate=True, n_buckets=args.n_buckets)
         ps.net.g.normal_()
-        ours_ms = timed(lambda: ps.train_step(None, None), args.iters, world)
+        if not args.no_cuda_graph:          # the step's kernels as one graph launch: device-side latency, not host launch rate
+            ps.train_step(None, None)
+            ps.enable_cuda_graph(None, None)
+
+        def ours_step():
+            ps.train_step(None, None)
+            ps.join()
+
+        ours_ms = timed(ours_step, args.iters, world)
+        timeline = None
+        if rank == 0:
+            ps.last_result()
+            timeline = ps.last_timing_us
+        nvls = bool(ps.nvls_gather)
         ps.close()
         del ps
         torch.cuda.empty_cache()
@@ -89,7 +104,9 @@ def main():
         del g, w, m
         link_bytes = (world - 1) * n * 2 * 2             # slots in + weights out at the master (bf16 both ways)
         row = {"bytes_bf16": size, "n_params": n, "n_gpus": world, "ours_us": ours_ms * 1e3, "ref_us": ref_ms * 1e3,
-               "speedup": ref_ms / ours_ms, "ours_master_link_GBps": link_bytes / (ours_ms * 1e-3) / 1e9 if world > 1 else None}
+               "speedup": ref_ms / ours_ms, "ours_master_link_GBps": link_bytes / (ours_ms * 1e-3) / 1e9 if world > 1 else None,
+               # fused update: fp32 master weights + momentum read and written, bf16 weights written (per parameter 18 B of HBM)
+               "ours_master_hbm_GBps": n * 18 / (ours_ms * 1e-3) / 1e9, "nvls_gather": nvls, "device_timeline_us": timeline}
         rows.append(row)
         if rank == 0:
             print("SWEEP " + json.dumps(row), flush=True)

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(512) ps_push_kernel(const float* __restrict__ 
 // before the step is released, so updating bucket b mid-backward cannot disturb a worker that still needs the
 // old weights for its data gradients.
 // ------------------------------------------------------------------------------------------------
-enum { CTL_DONE = 2, CTL_ERR = 4, CTL_TOTAL = 6, CTL_T0 = 8, CTL_TK = 10, CTL_BMASK = 64, CTL_BCNT = 128 };
+enum { CTL_DONE = 2, CTL_ERR = 4, CTL_TOTAL = 6, CTL_T0 = 8, CTL_TK = 10, CTL_BMASK = 64, CTL_BCNT = 128, CTL_SELECTED = 192 };
 
 struct MasterArgs {
     pdnn_ps_master_t a;
@@ -143,6 +143,10 @@ __global__ void __launch_bounds__(32) ps_bucket_wait_kernel(const __grid_constan
     const uint32_t count = (uint32_t)__popc(mask);
     if (is_last && lane < a.n_workers && !((mask >> lane) & 1u) && a.worker_closed[lane] != nullptr)
         st_release_sys(a.worker_closed[lane], cur_step);          // straggler kill: this step is closed for you
+    if (is_last && lane < a.n_workers && lane < 16) {      // how often each worker was among the first k (since the run began)
+        ctl[CTL_SELECTED + lane] += (mask >> lane) & 1u;
+        margs.result[56 + lane] = ctl[CTL_SELECTED + lane];
+    }
     if (lane == 0) {
         ctl[CTL_BMASK + b] = err ? 0u : mask;
         ctl[CTL_BCNT + b] = err ? 0u : count;
@@ -402,6 +406,47 @@ __global__ void __launch_bounds__(512) p2p_copy_kernel(const uint4* __restrict__
     for (; i < n16; i += nth) st_na_v4(dst + i, ld_nc_v4(src + i));
 }
 
+// ---- link microbenchmarks: multicast store, in-switch load-reduce, flag round trip -------------------
+__global__ void __launch_bounds__(512) mc_store_kernel(const uint4* __restrict__ src, uint4* mc_dst, long long n16) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    for (long long i = tid; i < n16; i += nth) multimem_st_v4(mc_dst + i, src[i]);
+}
+__global__ void __launch_bounds__(512) mc_ld_reduce_kernel(const float* mc_src, float4* __restrict__ dst, long long n4) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    for (long long base = tid; base < n4; base += nth * 4) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long i = base + u * nth;
+            if (i < n4)
+                asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                             : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(mc_src + i * 4) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long i = base + u * nth;
+            if (i < n4) dst[i] = v[u];
+        }
+    }
+}
+// Two GPUs bounce a counter: the initiator stores i into the peer's word and waits for the echo in its own.
+__global__ void flag_pingpong_kernel(uint32_t* mine, uint32_t* peers, int iters, int initiator, uint32_t base, unsigned long long* out_ns) {
+    const uint64_t t0 = globaltimer_ns();
+    for (int i = 1; i <= iters; ++i) {
+        const uint32_t v = base + (uint32_t)i;
+        if (initiator) {
+            st_release_sys(peers, v);
+            while (ld_acquire_sys(mine) != v) {}
+        } else {
+            while (ld_acquire_sys(mine) != v) {}
+            st_release_sys(peers, v);
+        }
+    }
+    if (out_ns != nullptr) *out_ns = globaltimer_ns() - t0;
+}
+
 }  // namespace pdnn
 
 using namespace pdnn;
@@ -553,6 +598,31 @@ extern "C" int pdnn_p2p_copy(const void* src, void* dst, long long nbytes, int m
     PDNN_REQUIRE(nbytes % 16 == 0, "p2p_copy: size must be a multiple of 16 bytes");
     const int grid = ps_grid(nbytes / 16 / 4 + 1, 512, max_ctas > 0 ? max_ctas : 148 * 2);
     p2p_copy_kernel<<<grid, 512, 0, ST(stream)>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), nbytes / 16);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pdnn_mc_store(const void* src, void* mc_dst, long long nbytes, int max_ctas, void* stream) {
+    PDNN_REQUIRE(nbytes > 0 && nbytes % 16 == 0 && mc_dst != nullptr, "mc_store: needs a multicast address and a multiple of 16 bytes");
+    mc_store_kernel<<<ps_grid(nbytes / 16 + 1, 512, max_ctas > 0 ? max_ctas : 148 * 2), 512, 0, ST(stream)>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(mc_dst), nbytes / 16);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+extern "C" int pdnn_mc_ld_reduce_f32(const void* mc_src, float* dst, long long n, int max_ctas, void* stream) {
+    PDNN_REQUIRE(n > 0 && n % 4 == 0 && mc_src != nullptr, "mc_ld_reduce: needs a multicast address and a multiple of 4 elements");
+    mc_ld_reduce_kernel<<<ps_grid(n / 16 + 1, 512, max_ctas > 0 ? max_ctas : 148 * 2), 512, 0, ST(stream)>>>(
+        reinterpret_cast<const float*>(mc_src), reinterpret_cast<float4*>(dst), n / 4);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+extern "C" int pdnn_flag_pingpong(uint32_t* mine, uint32_t* peers, int iters, int initiator, uint32_t base, unsigned long long* out_ns,
+                                  void* stream) {
+    PDNN_REQUIRE(mine != nullptr && peers != nullptr && iters > 0, "flag_pingpong: bad arguments");
+    flag_pingpong_kernel<<<1, 1, 0, ST(stream)>>>(mine, peers, iters, initiator, base, out_ns);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

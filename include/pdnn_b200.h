@@ -265,7 +265,8 @@ typedef struct pdnn_ps_master {
  * the hard timeout expired before k arrivals), [4]=microseconds from the start of the step to the k-th arrival of the
  * last bucket, [5]=microseconds from that arrival to the release (the un-overlapped tail), [6]=gradient sets applied
  * since the run began, [7]=n_buckets, [8+b]=mask of bucket b, [40+b]=microseconds into the step at which bucket b
- * had its k arrivals (device %globaltimer). */
+ * had its k arrivals (device %globaltimer), [56+w]=number of steps in which worker w was among the first k of the last
+ * bucket since the run began. */
 int pdnn_ps_master_step(const pdnn_ps_master_t* args, uint32_t* result, void* stream);
 /* The {wait, reduce} pair of ONE bucket of that step; pdnn_ps_master_step(args) == for b in 0..n_buckets-1 this call.
  * Buckets must be enqueued in order on one stream. */
@@ -318,6 +319,14 @@ int pdnn_enable_peer_access(int peer_device);
 
 /* Link microbenchmarks: copy n bytes local->dst (peer) with 16-byte stores. */
 int pdnn_p2p_copy(const void* src, void* dst, long long nbytes, int max_ctas, void* stream);
+/* n bytes local -> every member of a multicast group with multimem.st (one store, the switch replicates). */
+int pdnn_mc_store(const void* src, void* mc_dst, long long nbytes, int max_ctas, void* stream);
+/* dst[i] = sum over the multicast group's members of src[i] with multimem.ld_reduce (fp32, summed in the switch). */
+int pdnn_mc_ld_reduce_f32(const void* mc_src, float* dst, long long n, int max_ctas, void* stream);
+/* Flag round trip between two GPUs: `iters` release-store / acquire-load ping-pongs; *out_ns (device) = elapsed ns.
+ * Launch with initiator = 1 on one GPU and 0 on the other, `mine` local, `peers` the other GPU's word. */
+int pdnn_flag_pingpong(uint32_t* mine, uint32_t* peers, int iters, int initiator, uint32_t base, unsigned long long* out_ns,
+                       void* stream);
 
 /* fp32 variants used by the small-shape (LeNet / FC-MLP) path; same semantics as the bf16 entry points above. */
 int pdnn_nchw_f32_to_nhwc_f32(const float* x, float* y, int N, int C, int H, int W, int Cpad, void* stream);

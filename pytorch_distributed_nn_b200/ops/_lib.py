@@ -153,6 +153,9 @@ _SIGS = {
     "pdnn_set_word": [_P, _U, _P],
     "pdnn_set_abort_guard": [_P, _P],
     "pdnn_p2p_copy": [_P, _P, _L, _I, _P],
+    "pdnn_mc_store": [_P, _P, _L, _I, _P],
+    "pdnn_mc_ld_reduce_f32": [_P, _P, _L, _I, _P],
+    "pdnn_flag_pingpong": [_P, _P, _I, _I, _U, _P, _P],
     "pdnn_malloc": [C.POINTER(C.c_void_p), _L],
     "pdnn_free": [_P],
     "pdnn_ipc_get_handle": [_P, _P],

@@ -345,11 +345,11 @@ class B200ParameterServer:
         if self.is_master:
             self.flags[M_STEPW] = self.step
         self._graph_mode = True
-        if self.is_worker:
+        if self.is_worker and x_example is not None:
             self._gx = x_example.clone()
             self._gy = y_example.clone()
         else:
-            self._gx = self._gy = None
+            self._gx = self._gy = None          # no batch: master-only ranks, and the flat parameter vector of the comm sweep
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):                  # one eager step in graph mode (also the warm-up torch asks for)
@@ -399,8 +399,9 @@ class B200ParameterServer:
         """One synchronous-SGD step of this rank's role(s); advances the step counter."""
         if self._graph_ready:
             if self.is_worker:
-                self._gx.copy_(x_nchw_f32, non_blocking=True)
-                self._gy.copy_(labels, non_blocking=True)
+                if self._gx is not None:
+                    self._gx.copy_(x_nchw_f32, non_blocking=True)
+                    self._gy.copy_(labels, non_blocking=True)
                 self._graph.replay()
             if self._mgraph is not None:
                 with torch.cuda.stream(self.master_stream):
@@ -475,6 +476,7 @@ class B200ParameterServer:
                                "bucket_ready_us": r[40: 40 + nb]}
         self.last_bucket_masks = r[8: 8 + nb]
         self.total_sets_applied = r[6]
+        self.selected_counts = r[56: 56 + min(16, self.n_workers)]      # per worker: steps in which it was among the first k
         return tuple(r[:4])
 
     def master_state_dict(self):

@@ -92,3 +92,22 @@ def test_roofline_tool_groups_a_launch_list():
     t, w = m.main([os.path.join(root, "profiles", "launches_resnet18_b1024_v10.csv"), "--network", "ResNet18", "--batch", "1024"])
     assert t["batchnorm"] > 1000 and t["fprop+dgrad"] > t["wgrad"] > 1000        # microseconds
     assert abs(w["fprop"] / 1e12 - 1.137) < 0.01 and w["params"] > 11_000_000
+
+
+def test_data_prepare_synthesizes_real_file_formats_once(tmp_path):
+    """data_prepare writes the datasets in their on-disk formats; the package's readers then parse those files (the same
+    path real data takes) and a second run only verifies them."""
+    from pytorch_distributed_nn_b200.utils import data_prepare
+    from pytorch_distributed_nn_b200.utils.data import read_cifar10, read_mnist
+    md, cd = str(tmp_path / "m"), str(tmp_path / "c")
+    assert "absent" in data_prepare.prepare_mnist(md)["status"]
+    out = data_prepare.main(["--mnist-dir", md, "--cifar-dir", cd, "--synthesize"])
+    assert [r["status"] for r in out] == ["synthesized", "synthesized"]
+    assert out[0]["train"] == 60000 and out[0]["test"] == 10000 and out[1]["train"] == 50000 and out[1]["test"] == 10000
+    again = data_prepare.main(["--mnist-dir", md, "--cifar-dir", cd])
+    assert [r["status"] for r in again] == ["found", "found"]
+    a, b = read_cifar10(cd, worker_id=0), read_cifar10(cd, worker_id=0)
+    xa, ya = a.train.next_batch(16)
+    xb, yb = b.train.next_batch(16)
+    assert xa.shape == (16, 3, 32, 32) and (xa == xb).all() and (ya == yb).all()      # every rank reads the same files
+    assert read_mnist(md).train.images.shape[1:] == (1, 28, 28)
