@@ -19,6 +19,7 @@
 #include "../include/pdnn_b200.h"
 
 #include <mutex>
+#include <string.h>
 
 namespace pdnn {
 
@@ -54,6 +55,7 @@ struct GemmParams {
     float alpha;
     const float* bias;       // per output column, may be null
     const __nv_bfloat16* residual;  // optional bf16 [M][ldo] added before relu (bf16 out only)
+    int tma_store;           // bf16 output leaves through shared memory + TMA bulk tensor stores (set by launch_gemm)
     // straggler abort guard: if *guard_closed >= *guard_step the kernel returns immediately
     const uint32_t* guard_closed;
     const uint32_t* guard_step;
@@ -67,7 +69,10 @@ struct SmemLayout {
     static constexpr int B_LOCAL = HALF_B ? B_BYTES / 2 : B_BYTES;
     static constexpr int STAGE_BYTES = A_BYTES + B_LOCAL;
     static constexpr int STAGES = HALF_B ? (BN <= 128 ? 8 : 6) : ((BN <= 64) ? 8 : (BN <= 128 ? 6 : 4));
-    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+    // epilogue staging for TMA stores: per epilogue warp two slabs of 32 rows x 128 bytes (64 bf16 columns, 128B-swizzled)
+    static constexpr int EPI_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int EPI_BYTES = HALF_B ? 0 : 4 * 2 * 4096;
+    static constexpr int BAR_OFFSET = EPI_OFFSET + EPI_BYTES;
     static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
 };
 
@@ -78,7 +83,7 @@ struct SmemLayout {
 template <int AMODE, int BMODE, int BN, int CL = 1>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmO, const GemmParams p) {
     using L = SmemLayout<BN, CL == 3>;
     constexpr int STAGES = L::STAGES;
     constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
@@ -121,6 +126,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        if (CL == 1 && p.tma_store) tma_prefetch_desc(&tmO);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -303,6 +309,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int ew = warp & 3;           // TMEM lane quarter this warp may touch
         int acc = 0;
         uint32_t acc_phase = 0;
+        // TMA-store path: this warp's two staging slabs; a slab is rewritten only after the bulk store that read it is done
+        const bool tma_st = (CL == 1) && p.tma_store != 0;
+        const uint32_t slab_base = smem_base + L::EPI_OFFSET + (uint32_t)ew * 8192u;
+        uint32_t slab = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int rest = tile / p.k_splits;
             const int nt = CLUSTER ? rest / p.m_tiles : rest % p.n_tiles;
@@ -330,7 +340,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const int j = c * 32;
                     col0 = (r * p.S + (j >> 6)) * p.C + cb * 64 + (j & 63);
                 }
-                if (!row_ok || col0 >= p.N) continue;
+                if (tma_st) {
+                    if (col0 >= p.N) continue;          // warp-uniform (N % 64 == 0): both halves of a 64-column store or neither
+                    if ((c & 1) == 0) {                 // slab `slab` was last read by the store issued two stores ago
+                        if (lane == 0) bulk_wait_group_read<1>();
+                        __syncwarp();
+                    }
+                } else if (!row_ok || col0 >= p.N) continue;
                 float f[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.alpha;
@@ -346,7 +362,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     // 32-byte form: rows and both base pointers on 32-byte boundaries (CTA-uniform)
                     const bool vec32 = vec && ((p.ldo & 15) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 31) == 0) &&
                                        ((reinterpret_cast<uintptr_t>(p.residual) & 31) == 0);
-                    if (p.residual != nullptr) {
+                    if (p.residual != nullptr && row_ok) {
                         const __nv_bfloat16* rp = p.residual + row * p.ldo + col0;
                         if (vec32) {   // two 32-byte loads, both issued before the first use
                             const u32x8 r0 = ld_global_nc_256(rp), r1 = ld_global_nc_256(rp + 16);
@@ -376,7 +392,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                         for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
                     }
-                    if (vec32) {       // one full 32-byte sector per store
+                    if (tma_st) {
+                        // row `lane` of the slab, 16-byte chunk j of its 128 bytes lives at chunk j ^ (row & 7) (128B swizzle)
+                        const uint32_t row_addr = slab_base + slab * 4096u + (uint32_t)lane * 128u;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const uint32_t j = (uint32_t)((c & 1) * 4 + q);
+                            st_shared_v4(row_addr + ((j ^ ((uint32_t)lane & 7u)) << 4),
+                                         pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]), pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]),
+                                         pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]), pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]));
+                        }
+                        if (c & 1) {                    // 64 columns complete: hand the slab to the TMA engine
+                            fence_proxy_async_shared();
+                            __syncwarp();
+                            if (lane == 0) {
+                                tma_store_2d(&tmO, slab_base + slab * 4096u, col0 - 32, mt * BLOCK_M + ew * 32);
+                                bulk_commit_group();
+                            }
+                            slab ^= 1u;
+                        }
+                    } else if (vec32) {       // one full 32-byte sector per store
                         u32x8 w0, w1;
 #pragma unroll
                         for (int q = 0; q < 8; ++q) {
@@ -450,6 +485,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (tma_st && lane == 0) bulk_wait_group<0>();       // every store of this warp has left shared memory and landed
     }
 
     tc_fence_before();
@@ -533,7 +569,21 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     const int total = p.m_tiles * p.n_tiles * p.k_splits;
     int grid = total < num_sms() ? total : num_sms();
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
-    kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(tmA, tmB, p);
+    // bf16 outputs whose rows are whole 128-byte column groups leave as TMA bulk tensor stores of [32 rows][64 columns]
+    // boxes (full lines, coalesced by the copy engine) instead of one 32-byte sector per thread and instruction
+    GemmParams q = p;
+    CUtensorMap tmO;
+    memset(&tmO, 0, sizeof(tmO));
+    static const bool no_tma_store = getenv("PDNN_NO_TMA_STORE") != nullptr && getenv("PDNN_NO_TMA_STORE")[0] == '1';
+    q.tma_store = 0;
+    if (!no_tma_store && p.out_mode == 0 && p.out_remap == 0 && BMODE != OP_CONVMN && BMODE != OP_CONVMN_G3 && p.N % 64 == 0 &&
+        (p.ldo * 2) % 16 == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0) {
+        long long dims[2] = {p.N, p.M}, str[2] = {1, p.ldo};
+        int box[2] = {64, 32};
+        if (int rc = make_tmap_bf16(&tmO, p.out, 2, dims, str, box)) return rc;
+        q.tma_store = 1;
+    }
+    kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(tmA, tmB, tmO, q);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
@@ -569,7 +619,9 @@ static int launch_gemm_cluster(const CUtensorMap& tmA, const CUtensorMap& tmB, c
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas / 2 * 2;
     if (grid < 2) grid = 2;
     cfg.gridDim = dim3(grid);
-    PDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, p));
+    CUtensorMap tmO;                           // the pair schedule keeps the per-thread stores
+    memset(&tmO, 0, sizeof(tmO));
+    PDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, p));
     PDNN_COUNT_LAUNCH();
     return 0;
 }

@@ -71,6 +71,18 @@ __global__ void __launch_bounds__(512) ps_push_kernel(const float* __restrict__ 
     }
 }
 
+// Zero-copy form of the push: the gradient bucket already sits where the master reads it (the worker's fp32 gradient
+// buffer IS its slot, summed in the switch), so only the step-tagged arrival flag has to be published. The kernels that
+// wrote the bucket precede this one in the stream; the fence orders their global writes before the flag for a reader
+// on another GPU.
+__global__ void ps_publish_kernel(uint32_t* flag_peer, uint32_t step, const uint32_t* step_ptr, const uint32_t* guard_closed,
+                                  const uint32_t* guard_step) {
+    if (step_ptr != nullptr) step = ld_relaxed_sys(step_ptr);
+    if (guard_closed != nullptr && ld_relaxed_sys(guard_closed) >= ld_relaxed_sys(guard_step)) return;   // killed: nothing to announce
+    __threadfence_system();
+    st_release_sys(flag_peer, step);
+}
+
 // ------------------------------------------------------------------------------------------------
 // master: per gradient bucket, in arrival order: take the first k arrivals, reduce + 1/k + momentum SGD +
 // cast + broadcast; the last bucket also decides the kill set and releases the workers.
@@ -499,6 +511,15 @@ extern "C" int pdnn_ps_push_dev(const float* grad, void* slot_peer, long long n,
     if (int rc = push_counter(&counter)) return rc;
     const int grid = ps_grid(n / 8 + 1, 512, max_ctas);
     ps_push_kernel<<<grid, 512, 0, ST(stream)>>>(grad, slot_peer, n, slot_is_bf16, flag_peer, 0u, counter, guard_closed, guard_step, step_ptr);
+    PDNN_COUNT_LAUNCH();
+    PDNN_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int pdnn_ps_publish(uint32_t* flag_peer, uint32_t step, const uint32_t* step_ptr, const uint32_t* guard_closed,
+                               const uint32_t* guard_step, void* stream) {
+    PDNN_REQUIRE(flag_peer != nullptr, "ps_publish: missing flag");
+    ps_publish_kernel<<<1, 1, 0, ST(stream)>>>(flag_peer, step, step_ptr, guard_closed, guard_step);
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -210,6 +210,13 @@ int pdnn_ps_push(const float* grad, void* slot_peer, long long n, int slot_is_bf
                  uint32_t step, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
                  void* stream);
 
+/* Zero-copy push: the bucket is already where the master reads it (the worker's fp32 gradient buffer is its slot and the
+ * switch sums the workers' buffers), so only the arrival flag is published -- the weight-gradient kernels' own epilogues
+ * (red.add into that buffer) were the transfer. `step_ptr` non-NULL: the step tag is read from that device word.
+ * ref: communicator.Isend(grad, dest=0, tag=88+l) right after each layer's backward, resnet_split.py:244-250. */
+int pdnn_ps_publish(uint32_t* flag_peer, uint32_t step, const uint32_t* step_ptr, const uint32_t* guard_closed,
+                    const uint32_t* guard_step, void* stream);
+
 #define PDNN_MAX_RECEIVERS 24   /* workers + passive listeners (evaluator ranks) */
 #define PDNN_MAX_BUCKETS 32
 

@@ -315,7 +315,7 @@ class FlatParams:
     """A parameter vector without layers: the object the parameter-server kernels are benchmarked with
     (push / aggregate / broadcast sweeps, BASELINE config 5). ``train_step`` just declares every bucket ready."""
 
-    def __init__(self, n_params: int, dtype=BF16, device="cuda", n_buckets: int = 1, external_w=None):
+    def __init__(self, n_params: int, dtype=BF16, device="cuda", n_buckets: int = 1, external_w=None, external_g=None):
         self.name = f"Flat{n_params}"
         self.total = (n_params + ALIGN - 1) // ALIGN * ALIGN
         self.dtype = dtype
@@ -325,7 +325,7 @@ class FlatParams:
         dev = self.device
         self.w32 = torch.zeros(self.total, device=dev, dtype=F32)
         self.w = external_w if external_w is not None else torch.zeros(self.total, device=dev, dtype=dtype)
-        self.g = torch.zeros(self.total, device=dev, dtype=F32)
+        self.g = external_g if external_g is not None else torch.zeros(self.total, device=dev, dtype=F32)
         self.loss = torch.zeros(1, device=dev, dtype=F32)
         self.on_bucket = None
         self.layer_hook = None
@@ -367,7 +367,7 @@ class FlatParams:
 # builders (architectures: reference pytorch_code/model_ops/lenet.py:12-33, resnet.py:67-113; VGG is the
 # north-star addition, kuangliu CIFAR variant with BatchNorm)
 # -------------------------------------------------------------------------------------------------
-def build_lenet(batch, device="cuda", n_buckets=2, external_w=None) -> Network:
+def build_lenet(batch, device="cuda", n_buckets=2, external_w=None, external_g=None) -> Network:
     net = Network("LeNet", batch, (1, 28, 28), 10, dtype=F32, device=device)
     shp = (batch, 28, 28, 1)
     c1 = net.add(L.Conv2d(net, "conv1", 1, 20, 5, 1, 0, bias=True, in_shape=shp, first=True))
@@ -379,7 +379,7 @@ def build_lenet(batch, device="cuda", n_buckets=2, external_w=None) -> Network:
     fl = net.add(L.Flatten(net, "flatten", r2.out_shape))
     f1 = net.add(L.Linear(net, "fc1", 800, 500, fl.out_shape, hwc_from=(50, 4, 4)))
     net.add(L.Linear(net, "fc2", 500, 10, f1.out_shape))
-    net.finalize(n_buckets, external_w=external_w)
+    net.finalize(n_buckets, external_w=external_w, external_g=external_g)
     _set_bias_fan_in(net)
     return net
 
@@ -402,7 +402,7 @@ _RESNET_CFG = {
 }
 
 
-def build_resnet(name, batch, device="cuda", n_buckets=8, num_classes=10, external_w=None) -> Network:
+def build_resnet(name, batch, device="cuda", n_buckets=8, num_classes=10, external_w=None, external_g=None) -> Network:
     block, nblocks = _RESNET_CFG[name]
     net = Network(name, batch, (3, 32, 32), num_classes, dtype=BF16, device=device)
     shp = (batch, 32, 32, 3)
@@ -417,7 +417,7 @@ def build_resnet(name, batch, device="cuda", n_buckets=8, num_classes=10, extern
             cin = planes * block.expansion
     ap = net.add(L.GlobalAvgPool(net, "avgpool", shp))
     net.add(L.Linear(net, "linear", cin, num_classes, ap.out_shape))
-    net.finalize(n_buckets, external_w=external_w)
+    net.finalize(n_buckets, external_w=external_w, external_g=external_g)
     _set_bias_fan_in(net)
     return net
 
@@ -430,7 +430,7 @@ _VGG_CFG = {
 }
 
 
-def build_vgg(name, batch, device="cuda", n_buckets=8, num_classes=10, external_w=None) -> Network:
+def build_vgg(name, batch, device="cuda", n_buckets=8, num_classes=10, external_w=None, external_g=None) -> Network:
     net = Network(name, batch, (3, 32, 32), num_classes, dtype=BF16, device=device)
     shp = (batch, 32, 32, 3)
     cin = 3
@@ -451,7 +451,7 @@ def build_vgg(name, batch, device="cuda", n_buckets=8, num_classes=10, external_
             first = False
     fl = net.add(L.Flatten(net, "flatten", shp))
     net.add(L.Linear(net, "classifier", 512, num_classes, fl.out_shape))
-    net.finalize(n_buckets, external_w=external_w)
+    net.finalize(n_buckets, external_w=external_w, external_g=external_g)
     _set_bias_fan_in(net)
     for layer in net.layers:
         if isinstance(layer, L.BatchNorm):
@@ -459,7 +459,7 @@ def build_vgg(name, batch, device="cuda", n_buckets=8, num_classes=10, external_
     return net
 
 
-def build_mlp(dims, batch, device="cuda", n_buckets=4, activation="sigmoid", external_w=None) -> Network:
+def build_mlp(dims, batch, device="cuda", n_buckets=4, activation="sigmoid", external_w=None, external_g=None) -> Network:
     """Fully connected sigmoid MLP (reference: MPI_code/src/distributed_nn.cpp:35-47 784-500-500-800-800-200-100-100-10;
     pure_py_code/distributed_nn.py:41-96)."""
     net = Network("MLP" + "-".join(map(str, dims)), batch, (1, 1, dims[0]), dims[-1], dtype=F32, device=device)
@@ -470,23 +470,23 @@ def build_mlp(dims, batch, device="cuda", n_buckets=4, activation="sigmoid", ext
         if i < len(dims) - 2:
             act = net.add((L.Sigmoid if activation == "sigmoid" else L.ReLU)(net, f"act{i}", shp))
             shp = act.out_shape
-    net.finalize(n_buckets, external_w=external_w)
+    net.finalize(n_buckets, external_w=external_w, external_g=external_g)
     _set_bias_fan_in(net)
     return net
 
 
-def build_network(name: str, batch: int, device="cuda", n_buckets: int = 8, external_w=None) -> Network:
+def build_network(name: str, batch: int, device="cuda", n_buckets: int = 8, external_w=None, external_g=None) -> Network:
     key = name.replace("Split", "")
     if key.startswith("Flat"):
-        return FlatParams(int(key[4:]), BF16, device, n_buckets, external_w=external_w)
+        return FlatParams(int(key[4:]), BF16, device, n_buckets, external_w=external_w, external_g=external_g)
     if key in ("LeNet",):
-        return build_lenet(batch, device, min(n_buckets, 2), external_w=external_w)
+        return build_lenet(batch, device, min(n_buckets, 2), external_w=external_w, external_g=external_g)
     if key in ("ResNet", "Resnet"):
         key = "ResNet18"
     if key in _RESNET_CFG:
-        return build_resnet(key, batch, device, n_buckets, external_w=external_w)
+        return build_resnet(key, batch, device, n_buckets, external_w=external_w, external_g=external_g)
     if key in _VGG_CFG:
-        return build_vgg(key, batch, device, n_buckets, external_w=external_w)
+        return build_vgg(key, batch, device, n_buckets, external_w=external_w, external_g=external_g)
     if key in ("FC", "MLP"):
-        return build_mlp([784, 500, 500, 800, 800, 200, 100, 100, 10], batch, device, min(n_buckets, 4), external_w=external_w)
+        return build_mlp([784, 500, 500, 800, 800, 200, 100, 100, 10], batch, device, min(n_buckets, 4), external_w=external_w, external_g=external_g)
     raise ValueError(f"unknown network {name!r}")

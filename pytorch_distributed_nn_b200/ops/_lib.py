@@ -144,6 +144,7 @@ _SIGS = {
     "pdnn_ps_push": [_P, _P, _L, _I, _P, _U, _P, _P, _I, _P],
     "pdnn_ps_push_dev": [_P, _P, _L, _I, _P, _P, _P, _P, _I, _P],
     "pdnn_ps_wait_next": [_P, _P, _L, _P],
+    "pdnn_ps_publish": [_P, _U, _P, _P, _P, _P],
     "pdnn_ps_master_step": [C.POINTER(PSMaster), _P, _P],
     "pdnn_ps_master_bucket": [C.POINTER(PSMaster), _P, _I, _P],
     "pdnn_ps_fetch_weights": [_P, _P, _P, _L, _P, _U, _P],

@@ -150,7 +150,11 @@ class B200ParameterServer:
         self.land = [self.arena.tensor(o, self.wbytes, wdtype) for o in self.off_land]
         self.gslot = self.arena.tensor(self.off_gslot, slot_bytes, torch.bfloat16 if self.grad_bf16 else torch.float32)
         real_batch = batch if (self.is_worker or self.is_listener) else self._min_batch(network)
-        return build_network(network, real_batch, device=self.device, n_buckets=n_buckets)
+        # zero-copy push (fp32 wire + in-switch sum): the gradient buffer the weight-gradient kernels accumulate into IS the
+        # slot the master's multimem.ld_reduce reads, so a finished bucket only needs its flag published -- no push kernel
+        self.zero_copy = self.nvls_gather and not self.grad_bf16 and os.environ.get("PDNN_PS_ZERO_COPY", "1") != "0"
+        return build_network(network, real_batch, device=self.device, n_buckets=n_buckets,
+                             external_g=self.gslot if self.zero_copy else None)
 
     @staticmethod
     def _min_batch(network):
@@ -182,7 +186,10 @@ class B200ParameterServer:
             def on_bucket(b):
                 # every bucket carries its own step-tagged arrival flag: the master starts on bucket b while backward continues
                 flag = self._arrival_ptr + b.index * U32
-                if self._graph_mode:      # step tag read from the device word: the launch is replayable
+                if self.zero_copy:
+                    _lib.call("pdnn_ps_publish", flag, self.step, self.step_word.data_ptr() if self._graph_mode else None,
+                              self.closed_word.data_ptr(), self.step_word.data_ptr(), _lib.stream_ptr())
+                elif self._graph_mode:      # step tag read from the device word: the launch is replayable
                     _lib.call("pdnn_ps_push_dev", net.g.data_ptr() + b.start * 4, self._slot_ptr + b.start * self.slot_elem,
                               b.end - b.start, int(self.grad_bf16), flag, self.step_word.data_ptr(),
                               self.closed_word.data_ptr(), self.step_word.data_ptr(), 0, _lib.stream_ptr())
