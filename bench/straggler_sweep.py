@@ -8,7 +8,7 @@ the device.
         configs/interval_sweep/* configs/time_cdf/* [--iters 300] [--master-only] [--out results/straggler_study.json]
 
 Per config (rank 0 prints ``STUDY {json}``): images/sec from the gradient sets the master really applied, p50 / p99 /
-max of the device-timed step (max over ranks per step), how often each worker was among the first k, and the
+max of the device-timed step (release to release on the master's stream), how often each worker was among the first k, and the
 per-(worker, step) compute-time statistics the reference's driver plots (stdev, max, p80..p99, slowest-worker-per-
 iteration percentiles). ``--master-only`` makes GPU 0 a pure parameter server as in the reference (n = N-1 workers).
 """
@@ -69,7 +69,10 @@ def run_config(cfg, rank, world, dev, iters, master_only, warmup=5):
     if rank == 0:
         ps.last_result()
         mat = torch.stack(allt).cpu()                                   # [rank][iteration]
-        step_ms = mat.max(dim=0).values                                 # a step ends when its slowest rank has finished
+        # the step clock is the MASTER's: rank 0's interval ends when its last bucket has released the workers. (A max over
+        # ranks per step index would count one delay twice: ranks are up to a step apart, so the same wait shows up in
+        # neighbouring intervals of different ranks.)
+        step_ms = mat[0]
         total_s = float(mat.sum(dim=1).max()) / 1e3
         sets = ps.total_sets_applied - sets0
         workers = mat[(0 if colocate else 1):]                          # ranks that train
