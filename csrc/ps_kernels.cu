@@ -241,7 +241,7 @@ __device__ __forceinline__ void ps_poison(const pdnn_ps_master_t& a, uint32_t ma
 // gradient loads in flight (one multimem.ld_reduce round trip through the switch is ~2 us).
 #define PS_UNROLL 4
 template <bool BF16_SLOT>
-__global__ void __launch_bounds__(512) ps_bucket_reduce_kernel(const __grid_constant__ MasterArgs margs, int b, int is_last) {
+__global__ void __launch_bounds__(512, 2) ps_bucket_reduce_kernel(const __grid_constant__ MasterArgs margs, int b, int is_last) {
     const pdnn_ps_master_t& a = margs.a;
     const uint32_t cur_step = a.step_ptr != nullptr ? ld_relaxed_sys(a.step_ptr) : a.step;
     uint32_t* ctl = a.control;
@@ -257,24 +257,30 @@ __global__ void __launch_bounds__(512) ps_bucket_reduce_kernel(const __grid_cons
         const long long nth = (long long)gridDim.x * blockDim.x;
         const float lr = a.lr, mu = a.mu;
         for (long long base = i0 + tid; base < i1; base += nth * PS_UNROLL) {
-            float4 acc[PS_UNROLL];
+            // all loads of the PS_UNROLL elements are issued before any is used: the gradients come through the switch
+            // (microseconds), momentum and master weights from HBM; issued back to back their latencies overlap
+            float4 acc[PS_UNROLL], mom[PS_UNROLL], wgt[PS_UNROLL];
 #pragma unroll
             for (int u = 0; u < PS_UNROLL; ++u) {
                 const long long i = base + u * nth;
-                if (i < i1) acc[u] = ps_load_sum<BF16_SLOT>(a, mask, in_switch, i);
+                if (i < i1) {
+                    acc[u] = ps_load_sum<BF16_SLOT>(a, mask, in_switch, i);
+                    mom[u] = __ldcs(reinterpret_cast<const float4*>(a.momentum) + i);
+                    wgt[u] = __ldcs(reinterpret_cast<const float4*>(a.master_w) + i);
+                }
             }
 #pragma unroll
             for (int u = 0; u < PS_UNROLL; ++u) {
                 const long long i = base + u * nth;
                 if (i >= i1) continue;
                 if (a.poison_slots) ps_poison<BF16_SLOT>(a, mask, in_switch, i);
-                float4 m = reinterpret_cast<float4*>(a.momentum)[i];
-                float4 wv = reinterpret_cast<float4*>(a.master_w)[i];
+                float4 m = mom[u];
+                float4 wv = wgt[u];
                 m.x = mu * m.x + scale * acc[u].x; m.y = mu * m.y + scale * acc[u].y;
                 m.z = mu * m.z + scale * acc[u].z; m.w = mu * m.w + scale * acc[u].w;
                 wv.x -= lr * m.x; wv.y -= lr * m.y; wv.z -= lr * m.z; wv.w -= lr * m.w;
-                reinterpret_cast<float4*>(a.momentum)[i] = m;
-                reinterpret_cast<float4*>(a.master_w)[i] = wv;
+                __stcs(reinterpret_cast<float4*>(a.momentum) + i, m);
+                __stcs(reinterpret_cast<float4*>(a.master_w) + i, wv);
                 if (a.weights_are_bf16) {
                     uint2 u2;
                     u2.x = pack_bf16x2(wv.x, wv.y); u2.y = pack_bf16x2(wv.z, wv.w);
@@ -555,7 +561,7 @@ extern "C" int pdnn_ps_master_bucket(const pdnn_ps_master_t* args, uint32_t* res
     const int last = b == args->n_buckets - 1;
     ps_bucket_wait_kernel<<<1, 32, 0, ST(stream)>>>(m, b, b == 0, last);
     PDNN_COUNT_LAUNCH();
-    const int grid = ps_grid((args->bucket_hi[b] - args->bucket_lo[b]) / 4 / PS_UNROLL + 1, 512, args->max_ctas);
+    const int grid = ps_grid((args->bucket_hi[b] - args->bucket_lo[b]) / 4 / PS_UNROLL + 1, 512, args->max_ctas > 0 ? args->max_ctas : 296);
     if (args->slot_is_bf16) ps_bucket_reduce_kernel<true><<<grid, 512, 0, ST(stream)>>>(m, b, last);
     else ps_bucket_reduce_kernel<false><<<grid, 512, 0, ST(stream)>>>(m, b, last);
     PDNN_COUNT_LAUNCH();
