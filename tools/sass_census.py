@@ -13,16 +13,16 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "pytorch_distributed_nn_b200", "lib", "libpdnn_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-COLS = ["UTCHMMA", r"UTCHMMA\.2CTA", "LDTM", "UTMALDG", "UTMALDG.*MULTICAST", "UTCBAR", "SYNCS", "UCGABAR", "HMMA", "STG", r"STG\.E\.ENL2\.256", "LDG", "REDG?|ATOMG"]
+COLS = ["UTCHMMA", r"UTCHMMA\.2CTA", "LDTM", "UTMALDG", "UTMALDG.*MULTICAST", "UTMASTG", "UTCBAR", "SYNCS", "UCGABAR", "HMMA", "STG", r"STG\.E\.ENL2\.256", "LDG", "REDG?|ATOMG"]
 KEEP = {          # listing file -> regex on the demangled kernel name
     "conv_halo_kernel.sass": r"pdnn::conv_halo_kernel",
     "conv_halo_wgrad_kernel.sass": r"pdnn::conv_halo_wgrad_kernel",
     "conv_stem_kernel.sass": r"pdnn::conv_stem_kernel",
     "gemm_tcgen05_kernel_CONVK_K2D_256.sass": r"gemm_tcgen05_kernel<\(int\)2, \(int\)0, \(int\)256, \(int\)1>",
-    "gemm_tcgen05_kernel_CONVK_K2D_256_cluster2.sass": r"gemm_tcgen05_kernel<\(int\)2, \(int\)0, \(int\)256, \(int\)2>",
     "gemm_tcgen05_kernel_K2D_K2D_256_pair_2cta.sass": r"gemm_tcgen05_kernel<\(int\)0, \(int\)0, \(int\)256, \(int\)3>",
     "gemm_tcgen05_kernel_wgrad_G3_192.sass": r"gemm_tcgen05_kernel<\(int\)1, \(int\)4, \(int\)192, \(int\)1>",
-    "ps_master_step_kernel.sass": r"pdnn::ps_master_step_kernel",
+    "ps_bucket_reduce_kernel.sass": r"pdnn::ps_bucket_reduce_kernel<\(bool\)1>",
+    "ps_bucket_wait_kernel.sass": r"pdnn::ps_bucket_wait_kernel",
     "ps_push_kernel.sass": r"pdnn::ps_push_kernel",
 }
 
