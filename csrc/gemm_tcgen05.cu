@@ -62,7 +62,7 @@ struct GemmParams {
 };
 
 // HALF_B: CTA-pair mode, a stage holds the A tile and only this CTA's half of the B tile -> more stages fit
-template <int BN, bool HALF_B = false>
+template <int BN, bool HALF_B = false, bool NO_EPI = false>
 struct SmemLayout {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KiB
     static constexpr int B_BYTES = BN * BLOCK_K * 2;        // the whole N tile (the pair MMA sees it as two halves)
@@ -71,7 +71,9 @@ struct SmemLayout {
     static constexpr int STAGES = HALF_B ? (BN <= 128 ? 8 : 6) : ((BN <= 64) ? 8 : (BN <= 128 ? 6 : 4));
     // epilogue staging for TMA stores: per epilogue warp two slabs of 32 rows x 128 bytes (64 bf16 columns, 128B-swizzled)
     static constexpr int EPI_OFFSET = STAGES * STAGE_BYTES;
-    static constexpr int EPI_BYTES = HALF_B ? 0 : 4 * 2 * 4096;
+    // (none for the pair schedule and for the MN-major-B instantiations = weight gradients, whose fp32 output is accumulated
+    // with red.add: their smaller footprint lets a BatchNorm CTA of another stream share the SM)
+    static constexpr int EPI_BYTES = (HALF_B || NO_EPI) ? 0 : 4 * 2 * 4096;
     static constexpr int BAR_OFFSET = EPI_OFFSET + EPI_BYTES;
     static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;   // barriers + alignment slack
 };
@@ -84,7 +86,7 @@ template <int AMODE, int BMODE, int BN, int CL = 1>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmO, const GemmParams p) {
-    using L = SmemLayout<BN, CL == 3>;
+    using L = SmemLayout<BN, CL == 3, BMODE != OP_K2D>;
     constexpr int STAGES = L::STAGES;
     constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
@@ -310,7 +312,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int acc = 0;
         uint32_t acc_phase = 0;
         // TMA-store path: this warp's two staging slabs; a slab is rewritten only after the bulk store that read it is done
-        const bool tma_st = (CL == 1) && p.tma_store != 0;
+        const bool tma_st = (CL == 1) && (BMODE == OP_K2D) && p.tma_store != 0;
         const uint32_t slab_base = smem_base + L::EPI_OFFSET + (uint32_t)ew * 8192u;
         uint32_t slab = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -559,7 +561,7 @@ static int num_sms() {
 template <int AMODE, int BMODE, int BN>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int max_ctas,
                        cudaStream_t stream) {
-    using L = SmemLayout<BN>;
+    using L = SmemLayout<BN, false, BMODE != OP_K2D>;
     auto kern = gemm_tcgen05_kernel<AMODE, BMODE, BN>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -576,7 +578,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
     memset(&tmO, 0, sizeof(tmO));
     static const bool no_tma_store = getenv("PDNN_NO_TMA_STORE") != nullptr && getenv("PDNN_NO_TMA_STORE")[0] == '1';
     q.tma_store = 0;
-    if (!no_tma_store && p.out_mode == 0 && p.out_remap == 0 && BMODE != OP_CONVMN && BMODE != OP_CONVMN_G3 && p.N % 64 == 0 &&
+    if (!no_tma_store && p.out_mode == 0 && p.out_remap == 0 && BMODE == OP_K2D && p.N % 64 == 0 &&
         (p.ldo * 2) % 16 == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0) {
         long long dims[2] = {p.N, p.M}, str[2] = {1, p.ldo};
         int box[2] = {64, 32};

@@ -235,15 +235,8 @@ class Conv2d(Layer):
         F.im2col(x, self.k, self.k, self.stride, self.pad, k_pad=self.kpad, out=col)
         return col
 
-    # -- backward --------------------------------------------------------------------------------
-    def backward(self, dy, dx_residual=None):
-        """dy: [N,OH,OW,Cout]. Returns dx (or None for the first layer). ``dx_residual`` (implicit mode
-        only) is added to dx inside the dgrad epilogue."""
-        x = self.x
+    def _wgrad(self, x, dy, dy2, m):
         net = self.net
-        m = self.out_shape[0] * self.oh * self.ow
-        dy2 = dy.view(m, self.cout)
-        # ---- weight gradient first: the deepest parameters must leave for the master as early as possible
         if self.mode == "implicit":
             if self.halo_w:
                 F.conv_halo_wgrad(x, dy, out=self.weight.g.view(self.cout, self.k, self.k, self.cin))
@@ -266,6 +259,24 @@ class Conv2d(Layer):
             F.gemm_simt(dy2, col, trans_a=True, M=self.cout, N=self.kdim, K=m, out=self.weight.g.view(self.cout, self.kdim), accumulate=True)
         if self.bias is not None:
             F.col_sum(dy2, out=self.bias.g, accumulate=True)
+
+    # -- backward --------------------------------------------------------------------------------
+    def backward(self, dy, dx_residual=None):
+        """dy: [N,OH,OW,Cout]. Returns dx (or None for the first layer). ``dx_residual`` (implicit mode
+        only) is added to dx inside the dgrad epilogue."""
+        x = self.x
+        net = self.net
+        m = self.out_shape[0] * self.oh * self.ow
+        dy2 = dy.view(m, self.cout)
+        # ---- weight gradient first: the deepest parameters must leave for the master as early as possible. It only needs
+        # x and dy, like the data gradient below, so it goes to the network's side stream and runs next to the data gradient
+        # and the BatchNorm-backward passes that follow on the main stream (tensor-pipe bound next to HBM bound).
+        if net.overlap_wgrad and self.mode != "simt" and not self.first:
+            with torch.cuda.stream(net.side_stream()):
+                self._wgrad(x, dy, dy2, m)
+        else:
+            self._wgrad(x, dy, dy2, m)
+        if self.bias is not None:
             net.grad_ready(self.bias)
         net.grad_ready(self.weight)
         if self.first:

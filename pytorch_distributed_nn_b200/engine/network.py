@@ -66,6 +66,12 @@ class Network:
         self.bn_mask_from_x = os.environ.get("PDNN_BN_MASK_FROM_X", "1") == "1"   # BN backward without re-reading y (no residual)
         self.use_strided = os.environ.get("PDNN_NO_STRIDED") != "1"   # stride-2 convs as implicit GEMM (TMA element strides)
         self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
+        # weight-gradient kernels (tensor-pipe bound) on a side stream, next to the data-gradient + BatchNorm-backward chain
+        # (HBM bound) of the same layer: both only need dy. The side stream is joined before a bucket is pushed.
+        self.overlap_wgrad = os.environ.get("PDNN_WGRAD_OVERLAP", "1") == "1" and self.device.type == "cuda"
+        self._side = None
+        self._side_event = None
+        self._side_busy = False
 
     # ---- construction ---------------------------------------------------------------------------
     def add(self, layer):
@@ -258,10 +264,27 @@ class Network:
         for b in self.buckets:
             b.pending = len(b.param_ids)
 
+    def side_stream(self):
+        """Fork: returns the side stream, ordered behind everything enqueued on the current stream so far."""
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+            self._side_event = torch.cuda.Event()
+        cur = torch.cuda.current_stream(self.device)
+        self._side_event.record(cur)
+        self._side.wait_event(self._side_event)
+        self._side_busy = True
+        return self._side
+
+    def join_side(self):
+        if self._side_busy:
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._side_busy = False
+
     def grad_ready(self, p):
         b = self._param_bucket[p.index]
         b.pending -= 1
         if b.pending == 0 and self.on_bucket is not None:
+            self.join_side()            # weight gradients of this bucket may still be running on the side stream
             self.on_bucket(b)
 
     def stage_input(self, x_nchw_f32):
@@ -300,6 +323,7 @@ class Network:
             if self.layer_hook is not None:     # the reference sleeps before every backward layer (pure_py_code/distributed_worker.py:130-132)
                 self.layer_hook(idx)
             dy = layer.backward(dy)
+        self.join_side()
         self.pool_fresh = False
 
     def train_step(self, x_nchw_f32, labels):
