@@ -1,7 +1,7 @@
 // Stand-alone driver of the native FC parameter server (counterpart of MPI_code/src/distributed_nn.cpp and
 // single_machine_nn.cpp). Build: `make -C csrc distributed`; run: `make -C csrc distributed_run`.
 //   distributed_nn_native [--workers 6] [--collect 2] [--iters 100] [--batch 128] [--lr 0.001] [--data DIR]
-//                         [--delay-mask 0x7 --delay-us 500] [--no-shortcircuit] [--timeline] [--selftest]
+//                         [--delay-mask 0x7 --delay-us 500] [--no-shortcircuit] [--timeline] [--selftest] [--host-protocol]
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -16,6 +16,7 @@ int main(int argc, char** argv) {
     memcpy(c.dims, dims, sizeof(dims));
     c.batch = 128; c.lr = 1e-3f; c.n_workers = 6; c.n_to_collect = 2; c.n_train_iters = 100;
     c.shortcircuit = 1; c.with_evaluator = 1; c.eval_batches = 4; c.seed = 1; c.synthetic_examples = 8192;
+    c.device_protocol = 1;      // roles talk through the parameter-server kernels (device flags + peer stores)
     snprintf(c.out_dir, sizeof(c.out_dir), "outfiles");
     for (int i = 1; i < argc; ++i) {
         const char* a = argv[i];
@@ -31,6 +32,7 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--delay-us")) { c.delay_us_per_layer = atoll(v); ++i; }
         else if (!strcmp(a, "--no-shortcircuit")) c.shortcircuit = 0;
         else if (!strcmp(a, "--timeline")) c.generate_timeline = 1;
+        else if (!strcmp(a, "--host-protocol")) c.device_protocol = 0;
         else if (!strcmp(a, "--selftest")) {
             float l0, l1;
             int rc = pdnn_fc_ps_selftest(60, &l0, &l1);

@@ -13,10 +13,13 @@
 //   EvaluatorNN         evaluator_nn.h             -> fcps::evaluator_loop (outfiles/time_loss_out_<scheme>)
 //   mnist.h             IDX reader, /255, shuffle  -> fcps::load_mnist (+ synthetic fallback, loader self-test)
 //
-// B200 design: roles are host threads of ONE process, each bound to a GPU (all on one GPU when only one exists);
-// weights, slots and activations live in device memory; transfers between roles are device-to-device copies on the
-// sender's stream (NVLink peer copies across GPUs); the math runs on this library's kernels. Step tags live in host
-// atomics -- kernels never spin on one another, so the protocol is safe with any number of roles per GPU.
+// B200 design: roles are host threads of ONE process, each bound to a GPU (all on one GPU when only one exists); weights,
+// slots and activations live in device memory and the math runs on this library's kernels. Two transports:
+//   device protocol (default, cfg.device_protocol = 1): the roles talk through the parameter-server kernels of
+//     ps_kernels.cu -- per-(worker, layer) step-tagged device flags, peer stores (pdnn_ps_push), the per-bucket master
+//     (pdnn_ps_master_step), parity landing buffers + ready words, abort guards -- and the threads only enqueue;
+//   host protocol (cfg.device_protocol = 0): step tags in host atomics, condition variables, device-to-device copies on
+//     the sender's stream.
 #include "common.cuh"
 #include "../include/pdnn_b200.h"
 
@@ -155,14 +158,29 @@ struct Net {
     int* wrong = nullptr;
     std::atomic<bool>& failed;
     Net(const NNParams& prm, int dev, std::atomic<bool>& f) : p(prm), device(dev), failed(f) {}
-    void init() {
+    // flat = layer offsets into ONE weight and ONE gradient vector (device protocol: the parameter-server kernels work on
+    // flat buffers and address a layer as a bucket = an element range)
+    float* Wflat = nullptr;
+    float* Gflat = nullptr;
+    void init(const std::vector<long long>* flat_off = nullptr, long long flat_total = 0) {
         FC_CUDA(cudaSetDevice(device));
         FC_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
         const int L = p.n_layers();
         W.resize(L); G.resize(L); Z.resize(L); D.resize(L);
+        if (flat_off != nullptr) {
+            FC_CUDA(cudaMalloc(&Wflat, sizeof(float) * flat_total));
+            FC_CUDA(cudaMalloc(&Gflat, sizeof(float) * flat_total));
+            FC_CUDA(cudaMemset(Wflat, 0, sizeof(float) * flat_total));
+            FC_CUDA(cudaMemset(Gflat, 0, sizeof(float) * flat_total));
+        }
         for (int l = 0; l < L; ++l) {
-            FC_CUDA(cudaMalloc(&W[l], sizeof(float) * p.layer_elems(l)));
-            FC_CUDA(cudaMalloc(&G[l], sizeof(float) * p.layer_elems(l)));
+            if (flat_off != nullptr) {
+                W[l] = Wflat + (*flat_off)[l];
+                G[l] = Gflat + (*flat_off)[l];
+            } else {
+                FC_CUDA(cudaMalloc(&W[l], sizeof(float) * p.layer_elems(l)));
+                FC_CUDA(cudaMalloc(&G[l], sizeof(float) * p.layer_elems(l)));
+            }
             FC_CUDA(cudaMalloc(&Z[l], sizeof(float) * (size_t)p.batch * p.dims[l + 1]));
             FC_CUDA(cudaMalloc(&D[l], sizeof(float) * (size_t)p.batch * p.dims[l + 1]));
         }
@@ -173,7 +191,8 @@ struct Net {
     }
     void destroy() {
         cudaSetDevice(device);
-        for (auto v : {&W, &G, &Z, &D}) for (float* q : *v) cudaFree(q);
+        if (Wflat != nullptr) { cudaFree(Wflat); cudaFree(Gflat); for (auto v : {&Z, &D}) for (float* q : *v) cudaFree(q); }
+        else for (auto v : {&W, &G, &Z, &D}) for (float* q : *v) cudaFree(q);
         cudaFree(X); cudaFree(Y); cudaFree(loss); cudaFree(wrong);
         if (stream) cudaStreamDestroy(stream);
     }
@@ -449,6 +468,317 @@ static void master_loop(Board* b) {
     cudaStreamDestroy(stream);
 }
 
+
+// =================================================================================================================
+// Device protocol (cfg.device_protocol): the same roles driven by the parameter-server kernels of ps_kernels.cu instead of
+// host atomics, condition variables and cudaMemcpyPeerAsync. A layer is a bucket of ONE flat parameter vector:
+//   worker    pdnn_ps_wait_flag (ready >= step) -> per layer, just in time: pdnn_ps_fetch_weights of that layer's range
+//             from the landing buffer of the step's parity -> forward; backward layer by layer, each gradient pushed with
+//             pdnn_ps_push (peer stores + step-tagged flag (worker, layer)); with SHORTCIRCUIT the kernels carry the abort
+//             guard, so a worker the master has closed the step for falls through the rest of it (worker_nn.h:77-108);
+//   master    pdnn_ps_master_step: per layer in arrival order the first n_to_collect flags, mean over them, W -= lr * mean,
+//             new weights stored into every receiver's landing buffer, kill word + ready flag (sync_replicas_master_nn.h);
+//   evaluator a passive receiver: polls its ready word, snapshots the landing buffer of that parity, scores it.
+// The host threads only enqueue; nobody synchronises inside a step except the master's per-step read of the result block
+// (selection masks for the acceptance log and the timeline).
+// =================================================================================================================
+struct DevState {
+    int L = 0, n_workers = 0, n_recv = 0, stride = PDNN_MAX_BUCKETS;
+    std::vector<long long> off, len;      // per layer: offset into the flat vector (64-float aligned), padded length (x4)
+    long long total = 0;
+    int master_device = 0;
+    float* w_master = nullptr;            // master device: fp32 weights, momentum (unused: mu = 0), slots, control words
+    float* mom = nullptr;
+    std::vector<float*> slot;             // [worker] flat gradient slot on the master device
+    uint32_t* ctl = nullptr;              // control[256] | result[80] | arrival[n_workers][stride]
+    uint32_t* result = nullptr;
+    uint32_t* arrival = nullptr;
+    std::vector<int> recv_device;         // receivers: workers 0..n-1, then the evaluator
+    std::vector<float*> land[2];          // [parity][receiver] landing buffers on the receiver's device
+    std::vector<uint32_t*> flags;         // [receiver]: word 0 ready, 1 closed, 2 step
+    std::vector<int> batch_start;         // [worker * (iters + 2) + step]: first row of the batch the worker used at that step
+    std::atomic<int> inited{0};           // roles whose device buffers exist: the master launches nothing before all of them do
+                                          // (an allocation can block the host while a kernel that polls a flag is resident)
+};
+
+static void dev_worker_loop(Board* b, DevState* d, int w, int device, const Dataset* data) {
+    std::atomic<bool>& failed = b->failed;
+    Net net(b->p, device, failed);
+    net.init(&d->off, d->total);
+    const int L = d->L, iters = b->cfg.n_train_iters;
+    int cursor = (w * 997 * b->p.batch) % std::max(1, data->n - b->p.batch);
+    if (!failed.load()) {
+        // Dry run of every kernel this role will launch. With CUDA's lazy module loading the FIRST launch of a kernel loads
+        // it, and that load can wait for the whole context to drain -- which never happens while another role's kernel is
+        // polling a flag. So every role touches its kernels now, and nobody polls before all roles have done so.
+        int c0 = cursor;
+        pdnn_ps_wait_flag(d->flags[w] + 3, 0u, d->flags[w] + 4, 0, net.stream);
+        net.fill_batch(*data, &c0);
+        for (int l = 0; l < L; ++l) {
+            pdnn_ps_fetch_weights(d->land[0][w] + d->off[l], d->land[1][w] + d->off[l], net.W[l], sizeof(float) * d->len[l], nullptr, 1u, net.stream);
+            net.forward_layer(l);
+        }
+        net.output_delta();
+        for (int l = L - 1; l >= 0; --l) {
+            net.backward_layer(l);
+            pdnn_ps_push(net.G[l], net.G[l], b->p.layer_elems(l), 0, nullptr, 0u, nullptr, nullptr, 0, net.stream);   // onto itself: the slots stay zero for step 0
+        }
+        pdnn_delay(1000, nullptr, nullptr, net.stream);
+        pdnn_ps_publish(d->flags[w] + 5, 0u, nullptr, nullptr, nullptr, net.stream);
+        cudaStreamSynchronize(net.stream);
+    }
+    cudaDeviceSynchronize();
+    d->inited.fetch_add(1);
+    while (d->inited.load() < d->n_recv + 1 && !failed.load()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    if (failed.load()) return;
+    uint32_t* fl = d->flags[w];
+    const uint32_t* closed = b->cfg.shortcircuit ? fl + 1 : nullptr;
+    const uint32_t* stepw = b->cfg.shortcircuit ? fl + 2 : nullptr;
+    const long long delay_ns = ((b->cfg.delay_worker_mask >> w) & 1) ? b->cfg.delay_us_per_layer * 1000ll : 0;
+    pdnn_set_abort_guard(closed, stepw);                 // thread-local: the layer kernels this thread launches carry it
+    for (int step = 1; step <= iters && !failed.load(); ++step) {
+        if (pdnn_ps_wait_flag(fl, (uint32_t)step, fl + 2, 30000000000ll, net.stream)) { failed.store(true); break; }   // bounded: 30 s
+        int used = 0;
+        net.fill_batch(*data, &cursor, &used);
+        d->batch_start[(size_t)w * (iters + 2) + step] = used;
+        bool ok = true;
+        for (int l = 0; l < L && ok; ++l) {
+            // just-in-time fetch of layer l's weights from this step's landing buffer (worker_nn.h:56-74)
+            ok = pdnn_ps_fetch_weights(d->land[0][w] + d->off[l], d->land[1][w] + d->off[l], net.W[l], sizeof(float) * d->len[l], nullptr,
+                                       (uint32_t)step, net.stream) == 0 && net.forward_layer(l);
+        }
+        ok = ok && net.output_delta();
+        static const bool dbg = getenv("PDNN_FC_DEBUG") != nullptr;
+        if (dbg) { cudaError_t e = cudaStreamSynchronize(net.stream); fprintf(stderr, "fc_ps dbg: worker %d step %d forward done ok=%d cuda=%s\n", w, step, (int)ok, cudaGetErrorString(e)); }
+        for (int l = L - 1; l >= 0 && ok; --l) {
+            if (delay_ns > 0) pdnn_delay(delay_ns, closed, stepw, net.stream);      // injected straggler, on the device
+            // copy, then publish the (worker, layer) flag from a second tiny kernel: several workers may share one GPU here, and
+            // the single-kernel form keeps its grid-completion counter per device, not per stream
+            ok = net.backward_layer(l) &&
+                 pdnn_ps_push(net.G[l], d->slot[w] + d->off[l], b->p.layer_elems(l), 0, nullptr, (uint32_t)step, closed, stepw, 0, net.stream) == 0 &&
+                 pdnn_ps_publish(d->arrival + (size_t)w * d->stride + (L - 1 - l), (uint32_t)step, nullptr, closed, stepw, net.stream) == 0;
+            if (dbg) {
+                cudaError_t e = cudaStreamSynchronize(net.stream);
+                uint32_t fv = 0;
+                cudaMemcpy(&fv, d->arrival + (size_t)w * d->stride + (L - 1 - l), 4, cudaMemcpyDeviceToHost);
+                fprintf(stderr, "fc_ps dbg: worker %d step %d layer %d pushed ok=%d cuda=%s flag=%u\n", w, step, l, (int)ok, cudaGetErrorString(e), fv);
+            }
+        }
+        if (!ok) { fprintf(stderr, "fc_ps: worker %d failed at step %d: %s\n", w, step, pdnn_last_error()); failed.store(true); break; }
+    }
+    cudaStreamSynchronize(net.stream);
+    pdnn_set_abort_guard(nullptr, nullptr);
+    net.destroy();
+}
+
+static void dev_master_loop(Board* b, DevState* d) {
+    std::atomic<bool>& failed = b->failed;
+    FC_CUDA(cudaSetDevice(d->master_device));
+    cudaStream_t stream;
+    FC_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    const int L = d->L, iters = b->cfg.n_train_iters;
+    pdnn_ps_master_t a;
+    memset(&a, 0, sizeof(a));
+    for (int w = 0; w < d->n_workers; ++w) { a.slots[w] = d->slot[w]; a.worker_closed[w] = d->flags[w] + 1; }
+    for (int r = 0; r < d->n_recv; ++r) { a.recv_weights[0][r] = d->land[0][r]; a.recv_weights[1][r] = d->land[1][r]; a.recv_ready[r] = d->flags[r]; }
+    a.arrival_flags = d->arrival; a.arrival_stride = d->stride;
+    a.master_w = d->w_master; a.momentum = d->mom; a.control = d->ctl;
+    a.n = d->total; a.n_workers = d->n_workers; a.n_receivers = d->n_recv; a.k = b->cfg.n_to_collect;
+    a.slot_is_bf16 = 0; a.weights_are_bf16 = 0; a.avg_mode = 0; a.lr = b->p.lr; a.mu = 0.f;
+    a.n_buckets = L;
+    a.hard_timeout_ns = 10000000000ll;      // a bucket that never sees n_to_collect arrivals: give up after 10 s
+    for (int l = 0; l < L; ++l) { a.bucket_lo[L - 1 - l] = d->off[l]; a.bucket_hi[L - 1 - l] = d->off[l] + d->len[l]; }   // deepest layer arrives first
+    std::vector<uint32_t> res(80);
+    // Step 0 is the initial broadcast: every arrival word still holds 0, every slot is zero, so the master "aggregates" zero
+    // gradients, leaves the weights as they are, stores them into every receiver's landing buffer of parity 1 and publishes
+    // ready = 1 (the first step message + weight broadcast, sync_replicas_master_nn.h:46-60). It also loads the master's
+    // kernels before anybody polls (see dev_worker_loop).
+    a.step = 0u;
+    if (pdnn_ps_master_step(&a, d->result, stream)) { failed.store(true); }
+    FC_CUDA(cudaStreamSynchronize(stream));
+    while (d->inited.load() < d->n_recv && !failed.load()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    d->inited.fetch_add(1);                     // releases the other roles into step 1
+    const double t_begin = now_ms();
+    for (int step = 1; step <= iters && !failed.load(); ++step) {
+        const double t0 = now_ms();
+        if (b->cfg.generate_timeline) { b->timeline_ms.push_back(t0 - t_begin); b->timeline_step.push_back(step); b->timeline_who.push_back(-1); }
+        a.step = (uint32_t)step;
+        if (pdnn_ps_master_step(&a, d->result, stream)) { failed.store(true); break; }
+        FC_CUDA(cudaMemcpyAsync(res.data(), d->result, sizeof(uint32_t) * 80, cudaMemcpyDeviceToHost, stream));
+        FC_CUDA(cudaStreamSynchronize(stream));
+        if (res[3] == 0xDEADu) { fprintf(stderr, "fc_ps: master timed out at step %d\n", step); failed.store(true); break; }
+        // acceptance log in the order the master summed: bucket by bucket (layer L-1 first), workers by rank
+        for (int bkt = 0; bkt < L; ++bkt) {
+            const int l = L - 1 - bkt;
+            for (int w = 0; w < d->n_workers; ++w) {
+                if (!((res[8 + bkt] >> w) & 1u)) continue;
+                b->accepted++;
+                if (b->accept_log != nullptr && b->accept_n < b->accept_cap) {
+                    int* row = b->accept_log + 4 * b->accept_n++;
+                    row[0] = step; row[1] = w; row[2] = l; row[3] = d->batch_start[(size_t)w * (iters + 2) + step];
+                }
+                if (b->cfg.generate_timeline) { b->timeline_ms.push_back(t0 - t_begin + res[40 + bkt] / 1000.0); b->timeline_step.push_back(step); b->timeline_who.push_back(w); }
+            }
+        }
+        if (b->cfg.shortcircuit) b->abandoned_steps += __builtin_popcount(res[1]);       // workers told to drop the step
+        b->dropped_stale += (long long)__builtin_popcount(res[1]) * L;                    // their layer gradients never count
+        b->step_ms.push_back(now_ms() - t0);
+    }
+    cudaStreamDestroy(stream);
+}
+
+static void dev_evaluator_loop(Board* b, DevState* d, int device, const Dataset* data) {
+    std::atomic<bool>& failed = b->failed;
+    Net net(b->p, device, failed);
+    net.init(&d->off, d->total);
+    const int L = d->L, r_idx = d->n_workers, iters = b->cfg.n_train_iters;
+    if (!failed.load()) {                      // dry run: see dev_worker_loop
+        int c0 = 0;
+        net.fill_batch(*data, &c0);
+        for (int l = 0; l < L; ++l) net.forward_layer(l);
+        net.output_delta();
+        error_count_kernel<<<4, 128, 0, net.stream>>>(net.Z[L - 1], net.Y, b->p.batch, b->p.dims[L], net.wrong);
+        cudaStreamSynchronize(net.stream);
+    }
+    cudaDeviceSynchronize();
+    d->inited.fetch_add(1);
+    while (d->inited.load() < d->n_recv + 1 && !failed.load()) std::this_thread::sleep_for(std::chrono::microseconds(100));
+    if (failed.load()) return;
+    const double t0 = now_ms();
+    const std::string dir = b->cfg.out_dir[0] ? b->cfg.out_dir : "outfiles";
+    mkdir(dir.c_str(), 0755);
+    FILE* f = fopen((dir + "/time_loss_out_" + b->scheme).c_str(), "w");
+    uint32_t seen = 0;
+    while (!failed.load()) {
+        uint32_t r = 0;
+        cudaMemcpyAsync(&r, d->flags[r_idx], sizeof(r), cudaMemcpyDeviceToHost, net.stream);
+        cudaStreamSynchronize(net.stream);
+        if (r == seen || r == 0) { std::this_thread::sleep_for(std::chrono::microseconds(200)); continue; }
+        // snapshot the landing buffer of step r; the master refills it two steps later, so re-read the flag (seqlock)
+        cudaMemcpyAsync(net.Wflat, d->land[r & 1][r_idx], sizeof(float) * d->total, cudaMemcpyDeviceToDevice, net.stream);
+        uint32_t r2 = 0;
+        cudaMemcpyAsync(&r2, d->flags[r_idx], sizeof(r2), cudaMemcpyDeviceToHost, net.stream);
+        cudaStreamSynchronize(net.stream);
+        if (r2 != r) continue;                          // a newer step was released meanwhile: this parity may already be refilled
+        seen = r;
+        float loss_sum = 0.f; int wrong_sum = 0, n_seen = 0, cursor = 0, n_it = 0;
+        for (int it = 0; it < b->cfg.eval_batches && cursor + b->p.batch <= data->n; ++it, ++n_it) {
+            net.fill_batch(*data, &cursor);
+            for (int l = 0; l < L; ++l) net.forward_layer(l);
+            net.output_delta();
+            cudaMemsetAsync(net.wrong, 0, sizeof(int), net.stream);
+            error_count_kernel<<<4, 128, 0, net.stream>>>(net.Z[L - 1], net.Y, b->p.batch, b->p.dims[L], net.wrong);
+            float hl; int hw;
+            cudaMemcpyAsync(&hl, net.loss, sizeof(float), cudaMemcpyDeviceToHost, net.stream);
+            cudaMemcpyAsync(&hw, net.wrong, sizeof(int), cudaMemcpyDeviceToHost, net.stream);
+            cudaStreamSynchronize(net.stream);
+            loss_sum += hl; wrong_sum += hw; n_seen += b->p.batch;
+        }
+        const float loss = loss_sum / std::max(1, n_it), err = (float)wrong_sum / std::max(1, n_seen);
+        {
+            std::lock_guard<std::mutex> lk(b->mu);
+            b->eval_loss.push_back(loss);
+            b->eval_err.push_back(err);
+        }
+        if (f) { fprintf(f, "%u %.3f %.6f %.6f\n", r, now_ms() - t0, loss, err); fflush(f); }
+        if ((int)r > iters) break;                      // that was the final model
+    }
+    if (f) fclose(f);
+    net.destroy();
+}
+
+// Set up the device-protocol state from the host-protocol board (whose Wm[1][l] hold the initial weights), run the
+// three roles, leave the final weights in Wm[(iters + 1) & 1][l] where the caller reads them.
+static int run_device_protocol(Board* b, const Dataset* train, const Dataset* test, int n_dev) {
+    DevState st;
+    DevState* d = &st;
+    const int L = b->p.n_layers(), nw = b->n_workers, iters = b->cfg.n_train_iters;
+    d->L = L; d->n_workers = nw; d->n_recv = nw + (b->cfg.with_evaluator ? 1 : 0);
+    d->off.resize(L); d->len.resize(L);
+    long long off = 0;
+    for (int l = 0; l < L; ++l) {
+        d->off[l] = off;
+        d->len[l] = (b->p.layer_elems(l) + 3) / 4 * 4;
+        off += (d->len[l] + 63) / 64 * 64;
+    }
+    d->total = off;
+    d->batch_start.assign((size_t)nw * (iters + 2), 0);
+    auto dev_of_worker = [&](int w) { return n_dev > 1 ? 1 + w % (n_dev - 1) : 0; };
+    for (int w = 0; w < nw; ++w) d->recv_device.push_back(dev_of_worker(w));
+    if (b->cfg.with_evaluator) d->recv_device.push_back(n_dev > 1 ? n_dev - 1 : 0);
+    PDNN_CUDA_CHECK(cudaSetDevice(d->master_device));
+    PDNN_CUDA_CHECK(cudaMalloc(&d->w_master, sizeof(float) * d->total));
+    PDNN_CUDA_CHECK(cudaMalloc(&d->mom, sizeof(float) * d->total));
+    PDNN_CUDA_CHECK(cudaMemset(d->w_master, 0, sizeof(float) * d->total));
+    PDNN_CUDA_CHECK(cudaMemset(d->mom, 0, sizeof(float) * d->total));
+    const size_t ctl_words = 256 + 80 + (size_t)nw * d->stride;
+    PDNN_CUDA_CHECK(cudaMalloc(&d->ctl, sizeof(uint32_t) * ctl_words));
+    PDNN_CUDA_CHECK(cudaMemset(d->ctl, 0, sizeof(uint32_t) * ctl_words));
+    d->result = d->ctl + 256;
+    d->arrival = d->ctl + 256 + 80;
+    d->slot.assign(nw, nullptr);
+    for (int w = 0; w < nw; ++w) {
+        PDNN_CUDA_CHECK(cudaMalloc(&d->slot[w], sizeof(float) * d->total));
+        PDNN_CUDA_CHECK(cudaMemset(d->slot[w], 0, sizeof(float) * d->total));
+    }
+    for (int l = 0; l < L; ++l)
+        PDNN_CUDA_CHECK(cudaMemcpy(d->w_master + d->off[l], b->Wm[1][l], sizeof(float) * b->p.layer_elems(l), cudaMemcpyDeviceToDevice));
+    for (int par = 0; par < 2; ++par) d->land[par].assign(d->n_recv, nullptr);
+    d->flags.assign(d->n_recv, nullptr);
+    for (int r = 0; r < d->n_recv; ++r) {
+        PDNN_CUDA_CHECK(cudaSetDevice(d->recv_device[r]));
+        for (int par = 0; par < 2; ++par) {
+            PDNN_CUDA_CHECK(cudaMalloc(&d->land[par][r], sizeof(float) * d->total));
+            PDNN_CUDA_CHECK(cudaMemset(d->land[par][r], 0, sizeof(float) * d->total));
+        }
+        PDNN_CUDA_CHECK(cudaMalloc(&d->flags[r], 256));
+        PDNN_CUDA_CHECK(cudaMemset(d->flags[r], 0, 256));
+    }
+    // batches are copied from these host arrays every step: page-lock them so that the copies are true async DMA
+    cudaHostRegister(const_cast<float*>(train->images.data()), train->images.size() * sizeof(float), cudaHostRegisterDefault);
+    cudaHostRegister(const_cast<long long*>(train->labels.data()), train->labels.size() * sizeof(long long), cudaHostRegisterDefault);
+    if (test->images.data() != train->images.data()) {
+        cudaHostRegister(const_cast<float*>(test->images.data()), test->images.size() * sizeof(float), cudaHostRegisterDefault);
+        cudaHostRegister(const_cast<long long*>(test->labels.data()), test->labels.size() * sizeof(long long), cudaHostRegisterDefault);
+    }
+    cudaGetLastError();
+    // first-use allocations of the library (the push kernel's per-device counter block) happen now, not while kernels that
+    // spin on flags are resident
+    for (int r = 0; r < nw; ++r) {
+        PDNN_CUDA_CHECK(cudaSetDevice(d->recv_device[r]));
+        if (int rc = pdnn_ps_push(d->land[0][r], d->land[0][r], 4, 0, nullptr, 0, nullptr, nullptr, 1, nullptr)) return rc;
+    }
+    for (int i = 0; i < n_dev; ++i) { cudaSetDevice(i); cudaDeviceSynchronize(); }
+    std::vector<std::thread> threads;
+    for (int w = 0; w < nw; ++w) threads.emplace_back(dev_worker_loop, b, d, w, dev_of_worker(w), train);
+    if (b->cfg.with_evaluator) threads.emplace_back(dev_evaluator_loop, b, d, d->recv_device[nw], test);
+    std::thread master(dev_master_loop, b, d);
+    master.join();
+    if (b->failed.load()) {           // unblock whoever still waits on a flag: publish an impossible-to-miss ready value
+        const uint32_t big = 0x7fffffffu;
+        for (int r = 0; r < d->n_recv; ++r) { cudaSetDevice(d->recv_device[r]); cudaMemcpy(d->flags[r], &big, sizeof(big), cudaMemcpyHostToDevice); }
+    }
+    for (auto& t : threads) t.join();
+    cudaHostUnregister(const_cast<float*>(train->images.data()));
+    cudaHostUnregister(const_cast<long long*>(train->labels.data()));
+    if (test->images.data() != train->images.data()) {
+        cudaHostUnregister(const_cast<float*>(test->images.data()));
+        cudaHostUnregister(const_cast<long long*>(test->labels.data()));
+    }
+    cudaGetLastError();
+    PDNN_CUDA_CHECK(cudaSetDevice(d->master_device));
+    for (int l = 0; l < L; ++l)
+        PDNN_CUDA_CHECK(cudaMemcpy(b->Wm[(iters + 1) & 1][l], d->w_master + d->off[l], sizeof(float) * b->p.layer_elems(l), cudaMemcpyDeviceToDevice));
+    cudaFree(d->w_master); cudaFree(d->mom); cudaFree(d->ctl);
+    for (int w = 0; w < nw; ++w) cudaFree(d->slot[w]);
+    for (int r = 0; r < d->n_recv; ++r) {
+        cudaSetDevice(d->recv_device[r]);
+        cudaFree(d->land[0][r]); cudaFree(d->land[1][r]); cudaFree(d->flags[r]);
+    }
+    cudaSetDevice(d->master_device);
+    return 0;
+}
+
 }  // namespace fcps
 
 extern "C" int pdnn_fc_ps_run(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_result_t* res) {
@@ -523,12 +853,16 @@ extern "C" int pdnn_fc_ps_run_ex(const pdnn_fc_ps_config_t* cfg, pdnn_fc_ps_resu
     PDNN_REQUIRE(train.n >= b->p.batch, "fc_ps: dataset smaller than one batch");
 
     const double t0 = now_ms();
-    std::vector<std::thread> threads;
-    for (int w = 0; w < cfg->n_workers; ++w) threads.emplace_back(worker_loop, b, w, n_dev > 1 ? 1 + w % (n_dev - 1) : 0, &train);
-    if (cfg->with_evaluator) threads.emplace_back(evaluator_loop, b, n_dev > 1 ? n_dev - 1 : 0, &test);
-    std::thread master(master_loop, b);
-    master.join();
-    for (auto& t : threads) t.join();
+    if (cfg->device_protocol && L <= PDNN_MAX_BUCKETS && cfg->n_workers <= PDNN_MAX_WORKERS) {
+        if (int rc = run_device_protocol(b, &train, &test, n_dev)) return rc;
+    } else {
+        std::vector<std::thread> threads;
+        for (int w = 0; w < cfg->n_workers; ++w) threads.emplace_back(worker_loop, b, w, n_dev > 1 ? 1 + w % (n_dev - 1) : 0, &train);
+        if (cfg->with_evaluator) threads.emplace_back(evaluator_loop, b, n_dev > 1 ? n_dev - 1 : 0, &test);
+        std::thread master(master_loop, b);
+        master.join();
+        for (auto& t : threads) t.join();
+    }
     const double total = now_ms() - t0;
 
     memset(res, 0, sizeof(*res));
@@ -583,7 +917,7 @@ extern "C" int pdnn_fc_ps_selftest(int iters, float* first_loss, float* last_los
     memset(&c, 0, sizeof(c));
     c.n_dims = 3; c.dims[0] = 784; c.dims[1] = 100; c.dims[2] = 10;
     c.batch = 128; c.lr = 0.5f; c.n_workers = 1; c.n_to_collect = 1; c.n_train_iters = iters; c.with_evaluator = 1; c.eval_batches = 2;
-    c.seed = 7; c.synthetic_examples = 2048; c.max_devices = 1;
+    c.seed = 7; c.synthetic_examples = 2048; c.max_devices = 1; c.device_protocol = 1;
     snprintf(c.out_dir, sizeof(c.out_dir), "/tmp/pdnn_fc_selftest");
     pdnn_fc_ps_result_t r;
     if (int rc = pdnn_fc_ps_run(&c, &r)) return rc;

@@ -585,12 +585,14 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
 // ReLU / add / pooling
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void relu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+__global__ void relu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         y[i] = from_f<T>(fmaxf(to_f<T>(x[i]), 0.f));
 }
 template <typename T>
-__global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+__global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         dx[i] = to_f<T>(y[i]) > 0.f ? dy[i] : from_f<T>(0.f);
 }
@@ -846,12 +848,14 @@ __global__ void __launch_bounds__(256) sgd_momentum_kernel(float* __restrict__ w
 // sigmoid family
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void sigmoid_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+__global__ void sigmoid_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         y[i] = from_f<T>(1.f / (1.f + __expf(-to_f<T>(x[i]))));
 }
 template <typename T>
-__global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+__global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float s = to_f<T>(y[i]);
         dx[i] = from_f<T>(to_f<T>(dy[i]) * s * (1.f - s));
@@ -864,7 +868,8 @@ __global__ void sigmoid_bwd_kernel(const T* __restrict__ y, const T* __restrict_
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const float* __restrict__ A, long long sam, long long sak,
                                                         const float* __restrict__ B, long long sbk, long long sbn,
                                                         float* __restrict__ C, long long ldc, int M, int N, int K, float alpha,
-                                                        const float* __restrict__ bias, int relu, int accumulate, int k_per_split) {
+                                                        const float* __restrict__ bias, int relu, int accumulate, int k_per_split, NnGuard guard) {
+    NN_GUARD_RETURN(guard);
     __shared__ float As[16][64 + 4];
     __shared__ float Bs[16][64 + 4];
     const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
@@ -1067,20 +1072,20 @@ extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, c
 }
 extern "C" int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream) {
     if (n % 8 == 0) relu_fwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n / 8, nn_guard());
-    else relu_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n);
+    else relu_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
     if (n % 8 == 0) relu_bwd_vec8_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n / 8, nn_guard());
-    else relu_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n);
+    else relu_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_fwd_f32(const float* x, float* y, long long n, void* stream) {
-    relu_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n);
+    relu_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream) {
-    relu_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n);
+    relu_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_add_bf16(const void* a, const void* b, void* out, long long n, void* stream) {
@@ -1154,19 +1159,19 @@ extern "C" int pdnn_sgd_momentum(float* w, const float* g, float* m, void* w_bf1
     LAUNCH_OK();
 }
 extern "C" int pdnn_sigmoid_fwd(const void* x, void* y, long long n, void* stream) {
-    sigmoid_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n);
+    sigmoid_fwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(x), BF(y), n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_sigmoid_bwd(const void* y, const void* dy, void* dx, long long n, void* stream) {
-    sigmoid_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n);
+    sigmoid_bwd_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, ST(stream)>>>(CBF(y), CBF(dy), BF(dx), n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_sigmoid_fwd_f32(const float* x, float* y, long long n, void* stream) {
-    sigmoid_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n);
+    sigmoid_fwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(x, y, n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_sigmoid_bwd_f32(const float* y, const float* dy, float* dx, long long n, void* stream) {
-    sigmoid_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n);
+    sigmoid_bwd_kernel<float><<<grid_for(n, 256), 256, 0, ST(stream)>>>(y, dy, dx, n, nn_guard());
     LAUNCH_OK();
 }
 extern "C" int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, const float* B, int transB, long long ldb, float* C,
@@ -1186,7 +1191,7 @@ extern "C" int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, con
             grid.z = (K + k_per_split - 1) / k_per_split;
         }
     }
-    gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate, k_per_split);
+    gemm_simt_kernel<<<grid, 256, 0, ST(stream)>>>(A, sam, sak, B, sbk, sbn, C, ldc, M, N, K, alpha, bias, relu, accumulate, k_per_split, nn_guard());
     LAUNCH_OK();
 }
 

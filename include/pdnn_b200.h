@@ -205,7 +205,9 @@ int pdnn_gemm_simt_f32(const float* A, int transA, long long lda, const float* B
 /* Worker -> master gradient push (ref: communicator.Isend(grad, dest=0, tag=88+l),
  * pytorch_code/model_ops/lenet.py:119, distributed_worker.py:175). Copies (and optionally casts
  * fp32 -> bf16) `n` gradient elements into the master's slot for this worker (a peer pointer), then
- * publishes `step` in the master-side arrival flag with release.sys semantics. */
+ * publishes `step` in the master-side arrival flag with release.sys semantics. The grid-completion counter behind the
+ * flag is kept per DEVICE: pushes WITH a flag must not overlap on one GPU (one worker per GPU, the normal case). Several
+ * workers on one GPU push with flag_peer = NULL and publish with pdnn_ps_publish from the same stream. */
 int pdnn_ps_push(const float* grad, void* slot_peer, long long n, int slot_is_bf16, uint32_t* flag_peer,
                  uint32_t step, const uint32_t* guard_closed, const uint32_t* guard_step, int max_ctas,
                  void* stream);
@@ -378,6 +380,8 @@ typedef struct pdnn_fc_ps_config {
     int max_devices;            /* 0 = use every visible GPU */
     char data_dir[256];
     char out_dir[256];
+    int device_protocol;        /* 1: roles talk through the parameter-server kernels (per-(worker, layer) device flags, peer
+                                   stores, pdnn_ps_master_step per step); 0: host threads with atomics + peer copies */
 } pdnn_fc_ps_config_t;
 
 typedef struct pdnn_fc_ps_result {

@@ -62,7 +62,7 @@ class FcPsConfig(C.Structure):
         ("n_to_collect", C.c_int), ("n_train_iters", C.c_int), ("shortcircuit", C.c_int), ("generate_timeline", C.c_int),
         ("with_evaluator", C.c_int), ("eval_batches", C.c_int), ("delay_worker_mask", C.c_ulonglong),
         ("delay_us_per_layer", C.c_longlong), ("seed", C.c_uint), ("synthetic_examples", C.c_int), ("max_devices", C.c_int),
-        ("data_dir", C.c_char * 256), ("out_dir", C.c_char * 256),
+        ("data_dir", C.c_char * 256), ("out_dir", C.c_char * 256), ("device_protocol", C.c_int),
     ]
 
 

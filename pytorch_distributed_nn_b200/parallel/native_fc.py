@@ -18,7 +18,7 @@ from ..ops import _lib
 def run_native_fc_ps(dims=DIMS_CPP, batch=128, lr=1e-3, n_workers=6, n_to_collect=2, iters=100, shortcircuit=True,
                      timeline=False, evaluator=True, eval_batches=4, delay_workers=(), delay_us_per_layer=0, seed=1,
                      synthetic_examples=8192, max_devices=0, data_dir="", out_dir="outfiles", train=None, test=None,
-                     init_weights=None, want_weights=False, want_log=False) -> dict:
+                     init_weights=None, want_weights=False, want_log=False, device_protocol=True) -> dict:
     """``train`` / ``test``: optional ``(images float32 [n, dims[0]], labels int64 [n])`` CPU tensors; ``init_weights``:
     list of ``[(dims[l] + 1), dims[l+1]]`` float32 CPU tensors (bias = last row). With ``want_weights`` / ``want_log`` the
     result gains ``final_weights`` (same list form) and ``accept_log`` (rows ``(step, worker, layer, batch_start)`` in
@@ -36,6 +36,7 @@ def run_native_fc_ps(dims=DIMS_CPP, batch=128, lr=1e-3, n_workers=6, n_to_collec
     cfg.delay_worker_mask, cfg.delay_us_per_layer = mask, int(delay_us_per_layer)
     cfg.seed, cfg.synthetic_examples, cfg.max_devices = seed, synthetic_examples, max_devices
     cfg.data_dir, cfg.out_dir = data_dir.encode(), out_dir.encode()
+    cfg.device_protocol = int(device_protocol)
     res = _lib.FcPsResult()
     io = _lib.FcPsIO()
     keep = []

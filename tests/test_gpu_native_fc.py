@@ -61,6 +61,18 @@ def test_backup_workers_match_oracle_for_the_logged_selection(tmp_path):
     assert sum(1 for x in tl if x.endswith(" 1")) == iters  # one master mark per step
 
 
+def test_host_protocol_still_matches_its_oracle(tmp_path):
+    """The thread + condition-variable transport (device_protocol=False) stays available and correct."""
+    from pytorch_distributed_nn_b200.parallel.native_fc import oracle_replay, run_native_fc_ps
+    dims, batch, lr, iters = [784, 64, 10], 32, 0.3, 10
+    train, w0 = _problem(dims, 512, 9)
+    r = run_native_fc_ps(dims=dims, batch=batch, lr=lr, n_workers=3, n_to_collect=2, iters=iters, shortcircuit=True, out_dir=str(tmp_path),
+                         train=train, init_weights=w0, want_weights=True, want_log=True, device_protocol=False)
+    assert r["steps"] == iters
+    want = oracle_replay(dims, batch, lr, w0, train, r["accept_log"], iters)
+    assert _max_rel(r["final_weights"], want) < 2e-4
+
+
 def test_all_workers_collected_without_shortcircuit(tmp_path):
     from pytorch_distributed_nn_b200.parallel.native_fc import oracle_replay, run_native_fc_ps
     dims, batch, lr, iters = [784, 100, 10], 32, 0.3, 15
