@@ -229,13 +229,15 @@ class SyncReplicasMaster_NN(NN_Trainer):
         ps = self.ps
         timer = StepTimer(self.batch_size * ps.k)
         mark = {"t": time.perf_counter(), "step": ps.step - 1}
+        first_step = ps.step
 
         def on_log(i, loss):
             sel, kill, nrecv, st = ps.last_result()
             now = time.perf_counter()
             ms = (now - mark["t"]) * 1e3 / max(1, i - mark["step"])        # mean step time since the previous log line
             mark["t"], mark["step"] = now, i
-            timer.add(ms)
+            if i != first_step or self.max_steps == first_step:      # the first step carries one-time set-up (lazy kernel loads)
+                timer.add(ms)
             selected = [w for w in range(ps.n_workers) if sel >> w & 1]
             killed = [w for w in range(ps.n_workers) if kill >> w & 1]
             self.step_log.append((i, selected, killed, ms / 1e3))
