@@ -282,3 +282,30 @@ def test_polling_evaluator_restores_the_newest_checkpoint(tmp_path, capsys):
     assert "Precision @ 1" in capsys.readouterr().out
     # nothing new: a second poll evaluates nothing
     assert evaluate_checkpoints(str(tmp_path), "LeNet", data, eval_interval_secs=0.01, max_polls=2)[0][0] == 20
+
+
+def test_philox_known_answers_and_device_delay_replica():
+    """The host replica of the device-side delay draw: Philox4x32-10 known-answer vectors (Random123 kat_vectors) and the
+    properties a study relies on (deterministic in seed / worker / step / layer, rank subsets in the reference's spelling)."""
+    from pytorch_distributed_nn_b200.parallel.delays import philox4x32_10
+    assert philox4x32_10((0, 0, 0, 0), (0, 0)) == (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)
+    assert philox4x32_10((0xffffffff,) * 4, (0xffffffff, 0xffffffff)) == (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)
+    assert philox4x32_10((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0)) == \
+        (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)
+    pytest.importorskip("ctypes")
+    try:
+        from pytorch_distributed_nn_b200.parallel.delays import DeviceDelay
+        dd = DeviceDelay("uniform:lo=300:hi=1200:scale=0.005:seed=11")
+    except Exception as ex:          # the ctypes struct needs the built library
+        pytest.skip(f"library not built: {ex}")
+    a = [dd.sample_ns(w, s) for w in range(4) for s in range(1, 40)]
+    assert a == [DeviceDelay("uniform:lo=300:hi=1200:scale=0.005:seed=11").sample_ns(w, s) for w in range(4) for s in range(1, 40)]
+    assert all(1_500_000 <= v <= 6_000_000 for v in a) and len(set(a)) > 100
+    assert a != [DeviceDelay("uniform:lo=300:hi=1200:scale=0.005:seed=12").sample_ns(w, s) for w in range(4) for s in range(1, 40)]
+    sub = DeviceDelay("const:ranks=1,2,3:ms=500:scale=0.01")
+    assert [sub.sample_ns(w, 7) for w in range(5)] == [5_000_000] * 3 + [0, 0]
+    per_layer = DeviceDelay("exp:mean=1:per=layer:seed=2")
+    assert per_layer.per_layer and len({per_layer.sample_ns(0, 3, layer) for layer in range(8)}) == 8
+    sparse = DeviceDelay("exp:mean=1:p=0.25:seed=5")
+    hits = sum(1 for s in range(1, 801) if sparse.sample_ns(1, s) > 0)
+    assert 150 < hits < 250
