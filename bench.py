@@ -223,8 +223,8 @@ def main():
     chw = ps.net.in_chw
     gen = torch.Generator().manual_seed(1234 + rank)
     # synthetic CIFAR-10-shape data: raw 0..255 pixels like the reference reader (cifar10.py:167-199), 4 batches in rotation
-    host_x = [torch.empty(B, *chw).uniform_(0, 255, generator=gen) for _ in range(4)]
-    host_y = [torch.randint(0, 10, (B,), generator=gen) for _ in range(4)]
+    host_x = [torch.empty(B, *chw).uniform_(0, 255, generator=gen).pin_memory() for _ in range(4)]
+    host_y = [torch.randint(0, 10, (B,), generator=gen).pin_memory() for _ in range(4)]
     dev_x = [t.to(dev) for t in host_x]
     dev_y = [t.to(dev) for t in host_y]
 
@@ -350,7 +350,7 @@ def main():
                        "l2_policy": "working set (activations >> 126 MB L2 at batch 1024; 4 input batches rotate) exceeds L2"},
             "e2e": {"value": round(e2e_value, 1), "unit": "images/sec", "ms_per_step": round(e2e_ms / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "final_loss": losses[-1] if losses else None,
-                    "path": "B200ParameterServer.fit (the loop of the master / worker roles): pinned double-buffered H2D + loss D2H every step"},
+                    "path": "B200ParameterServer.fit (the loop of the master / worker roles): every step's batch pinned host -> device on a side stream, every step's loss device -> pinned host and read by the host one step later"},
             "gpu_launches": int(launches),
             "gpu_launches_per_step": round(launches / args.steps, 1),
             "gradient_sets_applied": {"resident": sets_resident, "e2e": sets_e2e},

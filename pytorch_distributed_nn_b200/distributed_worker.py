@@ -173,6 +173,8 @@ class DistributedWorker(NN_Trainer):
     def _train_b200(self, train_loader):
         """Same loop as the master's colocated worker: ``B200ParameterServer.fit`` (pinned staging + CUDA-graph replay)."""
         ps = self.ps
+        if train_loader is not None and hasattr(train_loader, "pin_memory"):
+            train_loader.pin_memory()           # batches are then DMA'd from where they are
         steps = self.max_steps or 20000
 
         def on_log(i, loss):

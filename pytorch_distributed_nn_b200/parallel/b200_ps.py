@@ -439,10 +439,19 @@ class B200ParameterServer:
             bx, by = train_loader.next_batch(self.batch_size)
             if getattr(self, "_stager", None) is None:
                 self._stager = PinnedBatchStager(tuple(bx.shape), dev)
-                self._loss_host = torch.zeros(1).pin_memory()
-            stager, loss_host = self._stager, self._loss_host
+            stager = self._stager
             slot = stager.stage(bx, by)
         losses = []
+        pending = None
+        loss_bufs = getattr(self, "_loss_bufs", None)
+        if loss_bufs is None and self.is_worker:
+            loss_bufs = self._loss_bufs = [torch.zeros(1).pin_memory(), torch.zeros(1).pin_memory()]
+
+        def collect(p):
+            step_i, event, host_buf = p
+            event.synchronize()
+            losses.append((step_i, float(host_buf)))
+
         while self.step <= last_step:
             i = self.step
             x = y = None
@@ -459,15 +468,30 @@ class B200ParameterServer:
                     slot = stager.stage(*train_loader.next_batch(self.batch_size))      # overlaps with the step just enqueued
             want_log = (should_log(i) if should_log is not None else i % log_interval == 0) or i == first or i == last_step
             if read_loss_every_step or want_log:
-                val = None
+                # Every step's loss is copied to pinned host memory right behind the step. It is READ one step late: the
+                # host first hands step i+1 to the device and then waits for step i's copy, so the device never idles
+                # for the launch latency of the next step. A log step (callback, checkpoint) is read at once.
+                ev = None
                 if loss is not None:
-                    loss_host.copy_(loss, non_blocking=True)
-                torch.cuda.current_stream(dev).synchronize()
-                if loss is not None:
-                    val = float(loss_host)
-                    losses.append((i, val))
-                if want_log and on_log is not None:
-                    on_log(i, val)
+                    buf = loss_bufs[i & 1]
+                    buf.copy_(loss, non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(torch.cuda.current_stream(dev))
+                if pending is not None:
+                    collect(pending)
+                    pending = None
+                if want_log:
+                    torch.cuda.current_stream(dev).synchronize()
+                    val = None
+                    if loss is not None:
+                        val = float(buf)
+                        losses.append((i, val))
+                    if on_log is not None:
+                        on_log(i, val)
+                elif ev is not None:
+                    pending = (i, ev, buf)
+        if pending is not None:
+            collect(pending)
         torch.cuda.synchronize()               # both streams: the master's last release is part of the run
         return losses
 

@@ -227,6 +227,8 @@ class SyncReplicasMaster_NN(NN_Trainer):
         """The device backend's loop is ``B200ParameterServer.fit`` (pinned double-buffered input staging, the whole step
         replayed from a CUDA graph after two eager steps); this role logs, checkpoints and keeps the step records."""
         ps = self.ps
+        if train_loader is not None and hasattr(train_loader, "pin_memory"):
+            train_loader.pin_memory()           # batches are then DMA'd from where they are
         timer = StepTimer(self.batch_size * ps.k)
         mark = {"t": time.perf_counter(), "step": ps.step - 1}
         first_step = ps.step

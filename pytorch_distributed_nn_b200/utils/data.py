@@ -177,6 +177,19 @@ class _NextBatchDataset(torch.utils.data.Dataset):
         x, y = self.dataset.next_batch(batch_size)
         return torch.from_numpy(np.ascontiguousarray(x)), torch.from_numpy(np.ascontiguousarray(y))
 
+    def pin_memory(self):
+        """Page-lock the image / label arrays once (device backend): ``next_batch`` then hands out views of pinned memory
+        and the input staging copies them to the GPU without an intermediate host copy. After an epoch's reshuffle the
+        arrays are new (pageable) ones and staging falls back to its own pinned buffers."""
+        ds = self.dataset
+        if not torch.cuda.is_available() or getattr(ds, "_pinned", None) is not None:
+            return self
+        imgs = torch.from_numpy(np.ascontiguousarray(ds._images, dtype=np.float32)).pin_memory()
+        labs = torch.from_numpy(np.ascontiguousarray(ds._labels, dtype=np.int64)).pin_memory()
+        ds._pinned = (imgs, labs)
+        ds._images, ds._labels = imgs.numpy(), labs.numpy()
+        return self
+
 
 class MNISTDataset(_NextBatchDataset):
     pass
@@ -220,17 +233,27 @@ class PinnedBatchStager:
         self.free = [torch.cuda.Event() for _ in range(n_buffers)]
         self.i = 0
         self.used = [False] * n_buffers
+        self._src = [None] * n_buffers
 
     def stage(self, x, y):
         b = self.i % len(self.hx)
         self.i += 1
-        self.hx[b].view(-1).copy_(x.reshape(-1))          # same element count, any host layout ([B,1,28,28] for a [B,784] net)
-        self.hy[b].copy_(y)
+        # a batch that already lives in page-locked memory (a pinned data set, see _NextBatchDataset.pin_memory) is copied to
+        # the device straight from where it is; anything else goes through this stager's own pinned buffers first
+        direct = (x.dtype == torch.float32 and y.dtype == torch.long and x.is_contiguous() and y.is_contiguous()
+                  and x.numel() == self.hx[b].numel() and x.is_pinned() and y.is_pinned())
+        if direct:
+            sx, sy = x.reshape(self.hx[b].shape), y
+            self._src[b] = (sx, sy)                          # keep the source alive until the copy has run
+        else:
+            self.hx[b].view(-1).copy_(x.reshape(-1))         # same element count, any host layout ([B,1,28,28] for a [B,784] net)
+            self.hy[b].copy_(y)
+            sx, sy = self.hx[b], self.hy[b]
         with torch.cuda.stream(self.stream):
             if self.used[b]:
                 self.stream.wait_event(self.free[b])
-            self.dx[b].copy_(self.hx[b], non_blocking=True)
-            self.dy[b].copy_(self.hy[b], non_blocking=True)
+            self.dx[b].copy_(sx, non_blocking=True)
+            self.dy[b].copy_(sy, non_blocking=True)
             self.ready[b].record(self.stream)
         return b
 
