@@ -177,11 +177,19 @@ class DistributedWorker(NN_Trainer):
             train_loader.pin_memory()           # batches are then DMA'd from where they are
         steps = self.max_steps or 20000
 
+        eval_freq = int(self.kwargs.get("eval_freq", 0) or 0)
+        # a master-only rank 0 never runs forward, so its BatchNorm running statistics would stay at their initial values in
+        # every checkpoint: the first worker hands its own over whenever the master is about to write one
+        ships_bn = (not self.colocate) and self.rank == 1 and bool(self.train_dir) and eval_freq > 0 and hasattr(ps.net, "bn_running_stats")
+
         def on_log(i, loss):
             self.history.append({"step": i, "loss": loss})
             print("Worker: {}, Cur Step: {}, Train Loss: {:.4f}".format(self.rank, i, loss), flush=True)
-
-        eval_freq = int(self.kwargs.get("eval_freq", 0) or 0)
+            if ships_bn and i % eval_freq == 0:
+                import torch.distributed as dist
+                flat = ps.net.bn_running_stats()
+                if flat.numel():
+                    dist.send(flat, dst=0)
 
         def should_log(i):     # the same predicate as the master's: every rank synchronises with its device at the same steps
             return i % self.log_interval == 0 or (eval_freq and i % eval_freq == 0)

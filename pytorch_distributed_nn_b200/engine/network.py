@@ -68,6 +68,7 @@ class Network:
         self.use_halo = os.environ.get("PDNN_NO_HALO") != "1"   # halo-reuse conv kernel for the C<=128 stages
         # weight-gradient kernels (tensor-pipe bound) on a side stream, next to the data-gradient + BatchNorm-backward chain
         # (HBM bound) of the same layer: both only need dy. The side stream is joined before a bucket is pushed.
+        self.batches_tracked = 0        # training steps this network has run (BatchNorm num_batches_tracked of every layer)
         self.overlap_wgrad = os.environ.get("PDNN_WGRAD_OVERLAP", "1") == "1" and self.device.type == "cuda"
         self._side = None
         self._side_event = None
@@ -210,7 +211,7 @@ class Network:
                 if bn is not None:
                     sd[bn.name + ".running_mean"] = bn.running_mean.clone()
                     sd[bn.name + ".running_var"] = bn.running_var.clone()
-                    sd[bn.name + ".num_batches_tracked"] = bn.num_batches_tracked.clone()
+                    sd[bn.name + ".num_batches_tracked"] = torch.tensor(int(self.batches_tracked), dtype=torch.long)
         return sd
 
     def load_state_dict(self, sd, strict: bool = True):
@@ -226,6 +227,25 @@ class Network:
                     if f"{layer.name}.{k}" in sd:
                         buf.copy_(sd[f"{layer.name}.{k}"])
         self.sync_compute_weights()
+
+    def bn_running_stats(self):
+        """All BatchNorm running means / variances / batch counters as ONE flat fp32 CPU tensor (and back): what a training
+        rank hands to a master-only rank before a checkpoint, since running statistics only exist where forward runs."""
+        parts = []
+        for layer in self._all_layers():
+            if isinstance(layer, L.BatchNorm):
+                parts += [layer.running_mean.float().reshape(-1).cpu(), layer.running_var.float().reshape(-1).cpu()]
+        return torch.cat(parts + [torch.tensor([float(self.batches_tracked)])]) if parts else torch.zeros(0)
+
+    def load_bn_running_stats(self, flat):
+        off = 0
+        for layer in self._all_layers():
+            if isinstance(layer, L.BatchNorm):
+                c = layer.c
+                layer.running_mean.copy_(flat[off: off + c])
+                layer.running_var.copy_(flat[off + c: off + 2 * c])
+                off += 2 * c
+        self.batches_tracked = int(flat[off])
 
     def _all_layers(self):
         for layer in self.layers:
@@ -328,6 +348,7 @@ class Network:
 
     def train_step(self, x_nchw_f32, labels):
         """forward + loss + backward; gradients end up in ``self.g`` (and buckets fire ``on_bucket``)."""
+        self.batches_tracked += 1
         self.zero_grad()
         self.forward(x_nchw_f32)
         self.loss_and_grad(labels)

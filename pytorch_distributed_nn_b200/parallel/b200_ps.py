@@ -371,6 +371,8 @@ class B200ParameterServer:
             self._graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._graph):
                 self._graph_loss = self._worker_part(self._gx, self._gy)
+            if hasattr(self.net, "batches_tracked"):
+                self.net.batches_tracked -= 1          # the capture enqueued nothing: not a training step
         if self.is_master and self.master_mode == "free":
             self._mgraph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self._mgraph, stream=self.master_stream):
@@ -410,6 +412,7 @@ class B200ParameterServer:
                     self._gx.copy_(x_nchw_f32, non_blocking=True)
                     self._gy.copy_(labels, non_blocking=True)
                 self._graph.replay()
+                self.net.batches_tracked = getattr(self.net, "batches_tracked", 0) + 1      # a replay does not pass Network.train_step
             if self._mgraph is not None:
                 with torch.cuda.stream(self.master_stream):
                     self._mgraph.replay()

@@ -246,6 +246,13 @@ class SyncReplicasMaster_NN(NN_Trainer):
             print("Master Step: {} selected: {} killed: {} Step Time: {:.6f}".format(i, selected, killed, ms / 1e3), flush=True)
             self.logger.log(step=i, selected=selected, killed=killed, step_ms=ms, loss=loss, device_timeline_us=ps.last_timing_us)
             if self.eval_freq and self.train_dir and i % self.eval_freq == 0:
+                if not ps.is_worker and hasattr(ps.net, "bn_running_stats"):
+                    # master-only rank: BatchNorm running statistics come from the first worker (distributed_worker.py)
+                    import torch.distributed as dist
+                    flat = ps.net.bn_running_stats()
+                    if flat.numel():
+                        dist.recv(flat, src=1)
+                        ps.net.load_bn_running_stats(flat.to(ps.device))
                 self.cur_step = i + getattr(self, "step_offset", 0)
                 self.save_checkpoint()
                 mark["t"] = time.perf_counter()

@@ -76,6 +76,12 @@ def test_device_sampled_delays_match_the_host_replica():
     assert 14.5 < s.elapsed_time(e) < 30.0
 
 
+def _close(a, b, tol=2e-3):
+    """Relative L2 distance: two runs of the same fp32 training differ by the order of their split-K atomics, and a max-pool
+    tie or ReLU gate that flips on a 1e-7 difference moves single weights by far more than an element-wise tolerance."""
+    return float((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-12)) < tol
+
+
 class _Batches:
     """Host batches handed out like utils.data datasets do (next_batch contract)."""
 
@@ -109,7 +115,7 @@ def test_fit_loop_with_pinned_staging_and_graph_equals_eager_steps():
     losses = b.fit(_Batches(xs, ys), 7, log_interval=3, on_log=lambda i, v: seen.append(i), read_loss_every_step=True)
     assert b._graph is not None and b.step == 8 and b.last_result() == (1, 0, 1, 7)
     assert [i for i, _ in losses] == list(range(1, 8)) and all(v == v for _, v in losses) and seen == [1, 3, 6, 7]
-    assert torch.allclose(b.net.w32, wa, rtol=1e-4, atol=1e-5) and torch.allclose(b.momentum, ma, rtol=1e-4, atol=1e-5)
+    assert _close(b.net.w32, wa) and _close(b.momentum, ma)
     b.close()
 
 
@@ -138,13 +144,13 @@ def test_resume_restores_weights_and_momentum(tmp_path):
     for x, y in zip(xs[3:], ys[3:]):
         c.train_step(x.cuda(), y.cuda())
     torch.cuda.synchronize()
-    assert torch.allclose(c.net.w32, wa, rtol=1e-4, atol=1e-5) and torch.allclose(c.momentum, ma, rtol=1e-4, atol=1e-5)
+    assert _close(c.net.w32, wa) and _close(c.momentum, ma)
     # without the sidecar the continuation differs: the test would not notice a dropped momentum otherwise
     d = B200ParameterServer("LeNet", 32, 0, 1, init_state_dict=sd, **kw)
     for x, y in zip(xs[3:], ys[3:]):
         d.train_step(x.cuda(), y.cuda())
     torch.cuda.synchronize()
-    assert not torch.allclose(d.net.w32, wa, rtol=1e-4, atol=1e-5)
+    assert not _close(d.net.w32, wa) and not _close(d.momentum, ma, 5e-2)      # a dropped momentum is far beyond the noise
     c.close()
     d.close()
 
@@ -228,3 +234,18 @@ def test_abort_guard_covers_the_layer_kernels():
     F.relu(x, out=y)
     torch.cuda.synchronize()
     assert torch.equal(y, torch.relu(x))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_master_only_checkpoint_carries_trained_batchnorm_statistics(tmp_path):
+    """Reference topology (rank 0 = parameter server only): the checkpoint's BatchNorm running statistics are the first
+    worker's, not the initial zeros / ones a rank that never runs forward would have."""
+    d = str(tmp_path)
+    r = _torchrun(2, ["distributed_nn.py", "--network", "VGG11", "--dataset", "Cifar10", "--synthetic", "--batch-size", "64", "--backend", "b200",
+                      "--max-steps", "6", "--eval-freq", "6", "--log-interval", "3", "--train-dir", d, "--lr", "0.01"], 29584)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    sd = torch.load(os.path.join(d, "model_step_6"))
+    means = [v for k, v in sd.items() if k.endswith("running_mean")]
+    vars_ = [v for k, v in sd.items() if k.endswith("running_var")]
+    assert means and all(float(m.abs().max()) > 0 for m in means) and any(float((v - 1).abs().max()) > 1e-3 for v in vars_)
+    assert all(int(v) == 6 for k, v in sd.items() if k.endswith("num_batches_tracked"))
