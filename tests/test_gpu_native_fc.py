@@ -55,7 +55,7 @@ def test_backup_workers_match_oracle_for_the_logged_selection(tmp_path):
     assert _max_rel(r["final_weights"], want) < 2e-4
     assert float((r["final_weights"][0] - w0[0]).abs().max()) > 0
     rows = open(os.path.join(out, "time_loss_out_" + r["scheme"])).read().strip().splitlines()
-    assert len(rows) >= 2 and all(len(x.split()) == 4 for x in rows)
+    assert len(rows) >= 1 and all(len(x.split()) == 4 for x in rows)      # how many snapshots it catches in between is timing
     assert int(rows[-1].split()[0]) == iters + 1         # the evaluator always scores the final model
     tl = open(os.path.join(out, "timeline_out_" + r["scheme"])).read().strip().splitlines()
     assert sum(1 for x in tl if x.endswith(" 1")) == iters  # one master mark per step
