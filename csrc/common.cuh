@@ -36,10 +36,42 @@ extern std::atomic<long long> g_pdnn_launches;
         }                                            \
     } while (0)
 
+
+// ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (default on, PDNN_PDL=0 turns it off): a kernel launched through pdnn_launch() may be scheduled while the
+// kernel before it on the stream is still draining, runs its prologue (barrier init, TMEM allocation, descriptor prefetch)
+// and then blocks in pdl_wait() until that kernel has completed and its writes are visible. Every kernel launched this
+// way calls pdl_wait() before it touches global memory that an earlier kernel may have written, then
+// pdl_launch_dependents() so that at most two kernels of the chain are in flight.
+// ------------------------------------------------------------------------------------------------
+#include <stdlib.h>
+#include <utility>
+static inline bool pdnn_pdl_enabled() {
+    static const bool on = !(getenv("PDNN_PDL") != nullptr && getenv("PDNN_PDL")[0] == '0');
+    return on;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t pdnn_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cfg.attrs = at;
+    cfg.numAttrs = pdnn_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Device helpers
 // ------------------------------------------------------------------------------------------------
 namespace pdnn {
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));

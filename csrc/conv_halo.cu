@@ -99,6 +99,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                 // everything above may overlap the tail of the previous kernel (programmatic dependent launch)
+    pdl_launch_dependents();
 
     // work split: CTA -> (output-channel block, strided subset of tiles)
     const int cb = blockIdx.x % p.n_cblocks;
@@ -354,7 +356,7 @@ static int conv_halo_fprop_impl(const void* x, const void* wgt, int batch, int H
     if (grid < p.n_cblocks) grid = p.n_cblocks;
     if (epi->max_ctas > 0 && grid > epi->max_ctas) grid = (epi->max_ctas / p.n_cblocks) * p.n_cblocks;
     if (grid < p.n_cblocks) grid = p.n_cblocks;
-    conv_halo_kernel<<<grid, HALO_THREADS, smem, stream>>>(tmX, tmW, p);
+    PDNN_CUDA_CHECK(pdnn_launch(conv_halo_kernel, dim3(grid), dim3(HALO_THREADS), (size_t)smem, stream, tmX, tmW, p));
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
@@ -467,6 +469,8 @@ conv_halo_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                 // everything above may overlap the tail of the previous kernel (programmatic dependent launch)
+    pdl_launch_dependents();
     const int halo_bytes = (p.Hc + 2) * p.Wp * 128;
     const int dy_tile_bytes = p.Hc * p.Wp * 128;
 
@@ -653,7 +657,7 @@ extern "C" int pdnn_conv_halo_wgrad_bf16(const void* x, const void* dy, int batc
         int a2 = grid * atoi(e) / 100 / combos * combos;
         if (a2 >= combos && grid - a2 >= combos) p.ctas_group_a = a2;
     }
-    conv_halo_wgrad_kernel<<<grid, HALO_THREADS, smem, stream>>>(tmDY, tmX, p);
+    PDNN_CUDA_CHECK(pdnn_launch(conv_halo_wgrad_kernel, dim3(grid), dim3(HALO_THREADS), (size_t)smem, stream, tmDY, tmX, p));
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -85,6 +85,8 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmW, const StemParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                 // everything above may overlap the tail of the previous kernel (programmatic dependent launch)
+    pdl_launch_dependents();
 
     if (warp < 4) {
         // ===================== gather producers =====================
@@ -321,7 +323,7 @@ extern "C" int pdnn_conv_stem_bf16(const void* x, const void* w_pad, int batch, 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int grid = p.total_tiles < sms ? p.total_tiles : sms;
     if (epi->max_ctas > 0 && grid > epi->max_ctas) grid = epi->max_ctas;
-    conv_stem_kernel<<<grid, STEM_THREADS, smem, stream>>>(tmW, p);
+    PDNN_CUDA_CHECK(pdnn_launch(conv_stem_kernel, dim3(grid), dim3(STEM_THREADS), (size_t)smem, stream, tmW, p));
     PDNN_COUNT_LAUNCH();
     PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;

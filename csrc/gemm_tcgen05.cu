@@ -155,6 +155,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (CLUSTER) cluster_sync_all();          // the peer's barriers exist before anything is sent to them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                               // the prologue above may overlap the tail of the previous kernel (programmatic dependent launch)
+    pdl_launch_dependents();
 
     const int total_tiles = p.m_tiles * p.n_tiles * p.k_splits;
     const int hw = p.H * p.W;
@@ -585,9 +587,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
         if (int rc = make_tmap_bf16(&tmO, p.out, 2, dims, str, box)) return rc;
         q.tma_store = 1;
     }
-    kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(tmA, tmB, tmO, q);
+    PDNN_CUDA_CHECK(pdnn_launch(kern, dim3(grid), dim3(NUM_THREADS), L::TOTAL, stream, tmA, tmB, tmO, q));
     PDNN_COUNT_LAUNCH();
-    PDNN_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 

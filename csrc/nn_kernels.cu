@@ -370,6 +370,8 @@ __global__ void __launch_bounds__(256, 2) bn_reduce_kernel(const __nv_bfloat16* 
                                                         float* __restrict__ out, long long M, int C, int relu,
                                                         const float* __restrict__ gamma, const float* __restrict__ beta, NnGuard guard) {
     NN_GUARD_RETURN(guard);
+    pdl_wait();
+    pdl_launch_dependents();
     extern __shared__ float sh[];   // [2][rows_per_iter][C]
     const int tpr = C / 8;                        // threads per row (<= 256)
     const int rpi = max(1, (int)blockDim.x / tpr); // rows per iteration
@@ -456,6 +458,8 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const __nv_bfloat16* 
                                                            float* __restrict__ mean_invstd, float* running_mean, float* running_var,
                                                            long long M, int C, float eps, float momentum, int relu, NnGuard guard) {
     NN_GUARD_RETURN(guard);
+    pdl_wait();
+    pdl_launch_dependents();
     const int tpr = C / 8;
     const int rpi = max(1, (int)blockDim.x / tpr);
     const int ct = threadIdx.x % tpr;
@@ -522,6 +526,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C, int relu,
                                                            const float* __restrict__ beta, NnGuard guard) {
     NN_GUARD_RETURN(guard);
+    pdl_wait();
+    pdl_launch_dependents();
     const int tpr = C / 8;
     const int rpi = max(1, (int)blockDim.x / tpr);
     const int ct = threadIdx.x % tpr;
@@ -1030,7 +1036,7 @@ extern "C" int pdnn_bn_fwd_stats(const void* x, float* stats, long long M, int C
     bn_reduce_cfg(C, &rpi, &smem);
     static const int wave = resident_blocks(bn_reduce_kernel<0>, 256, 16384);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, wave);
-    bn_reduce_kernel<0><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, nullptr, nullptr, stats, M, C, 0, nullptr, nullptr, nn_guard());
+    PDNN_CUDA_CHECK(pdnn_launch(bn_reduce_kernel<0>, dim3(grid), dim3(256), (size_t)smem, ST(stream), CBF(x), (const __nv_bfloat16*)nullptr, (const __nv_bfloat16*)nullptr, (const float*)nullptr, stats, M, C, 0, (const float*)nullptr, (const float*)nullptr, nn_guard()));
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
@@ -1040,8 +1046,8 @@ extern "C" int pdnn_bn_fwd_apply(const void* x, const float* stats, const float*
     int rpi_a; size_t smem_a;
     bn_reduce_cfg(C, &rpi_a, &smem_a);
     static const int wave = resident_blocks(bn_fwd_apply_kernel, 256, 0);
-    bn_fwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), stats, gamma, beta, CBF(residual), BF(y), mean_invstd,
-                                                                                     running_mean, running_var, M, C, eps, momentum, relu, nn_guard());
+    PDNN_CUDA_CHECK(pdnn_launch(bn_fwd_apply_kernel, dim3(grid_for((M + rpi_a - 1) / rpi_a, 1, wave)), dim3(256), (size_t)0, ST(stream), CBF(x), stats, gamma, beta,
+                                CBF(residual), BF(y), mean_invstd, running_mean, running_var, M, C, eps, momentum, relu, nn_guard()));
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean_invstd, float* sums, long long M,
@@ -1053,9 +1059,9 @@ extern "C" int pdnn_bn_bwd_reduce(const void* x, const void* y, const void* dy, 
     static const int wave1 = resident_blocks(bn_reduce_kernel<1>, 256, 16384), wave2 = resident_blocks(bn_reduce_kernel<2>, 256, 16384);
     const int grid = grid_for((M + rpi - 1) / rpi, 1, (relu && y == nullptr) ? wave2 : wave1);
     if (relu && y == nullptr)
-        bn_reduce_kernel<2><<<grid, 256, smem, ST(stream)>>>(CBF(x), nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard());
+        PDNN_CUDA_CHECK(pdnn_launch(bn_reduce_kernel<2>, dim3(grid), dim3(256), (size_t)smem, ST(stream), CBF(x), (const __nv_bfloat16*)nullptr, CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard()));
     else
-        bn_reduce_kernel<1><<<grid, 256, smem, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard());
+        PDNN_CUDA_CHECK(pdnn_launch(bn_reduce_kernel<1>, dim3(grid), dim3(256), (size_t)smem, ST(stream), CBF(x), CBF(y), CBF(dy), mean_invstd, sums, M, C, relu, gamma, beta, nn_guard()));
     LAUNCH_OK();
 }
 extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean_invstd, const float* gamma,
@@ -1066,8 +1072,8 @@ extern "C" int pdnn_bn_bwd_apply(const void* x, const void* y, const void* dy, c
     int rpi_a; size_t smem_a;
     bn_reduce_cfg(C, &rpi_a, &smem_a);
     static const int wave = resident_blocks(bn_bwd_apply_kernel, 256, 0);
-    bn_bwd_apply_kernel<<<grid_for((M + rpi_a - 1) / rpi_a, 1, wave), 256, 0, ST(stream)>>>(CBF(x), CBF(y), CBF(dy), mean_invstd, gamma, sums, BF(dx),
-                                                                                     BF(dresidual), dgamma, dbeta, M, C, relu, beta, nn_guard());
+    PDNN_CUDA_CHECK(pdnn_launch(bn_bwd_apply_kernel, dim3(grid_for((M + rpi_a - 1) / rpi_a, 1, wave)), dim3(256), (size_t)0, ST(stream), CBF(x), CBF(y), CBF(dy),
+                                mean_invstd, gamma, sums, BF(dx), BF(dresidual), dgamma, dbeta, M, C, relu, beta, nn_guard()));
     LAUNCH_OK();
 }
 extern "C" int pdnn_relu_fwd(const void* x, void* y, long long n, void* stream) {
