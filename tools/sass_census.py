@@ -13,7 +13,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "pytorch_distributed_nn_b200", "lib", "libpdnn_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-COLS = ["UTCHMMA", r"UTCHMMA\.2CTA", "LDTM", "UTMALDG", "UTMALDG.*MULTICAST", "UTMASTG", "UTCBAR", "SYNCS", "UCGABAR", "HMMA", "STG", r"STG\.E\.ENL2\.256", "LDG", "REDG?|ATOMG"]
+COLS = ["UTCHMMA", r"UTCHMMA\.2CTA", "LDTM", "UTMALDG", "UTMALDG.*MULTICAST", "UTMASTG", "UTCBAR", "SYNCS", "UCGABAR", "ACQBULK", "PREEXIT", "HMMA", "STG", r"STG\.E\.ENL2\.256", "LDG", "REDG?|ATOMG"]
 KEEP = {          # listing file -> regex on the demangled kernel name
     "conv_halo_kernel.sass": r"pdnn::conv_halo_kernel",
     "conv_halo_wgrad_kernel.sass": r"pdnn::conv_halo_wgrad_kernel",
@@ -48,7 +48,7 @@ def main():
     with open(os.path.join(OUT, "SUMMARY.md"), "w") as f:
         f.write("# SASS mnemonic census of libpdnn_b200.so (cuobjdump -sass, sm_100a)\n\n"
                 "`UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTMALDG` = TMA load (cp.async.bulk.tensor; `MULTICAST` = the cluster "
-                "form), `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier ops, `UCGABAR` = cluster barrier, `STG.E.ENL2.256` = 32-byte "
+                "form), `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier ops, `UCGABAR` = cluster barrier, `ACQBULK` / `PREEXIT` = griddepcontrol.wait / launch_dependents (programmatic dependent launch), `STG.E.ENL2.256` = 32-byte "
                 "stores. No `HMMA` (legacy mma.sync) appears anywhere. Regenerate with `python tools/sass_census.py`.\n\n")
         f.write("| kernel | #instr | " + " | ".join(c.replace("|", "/").replace("\\", "") for c in COLS) + " |\n")
         f.write("|---|---|" + "---|" * len(COLS) + "\n")
