@@ -309,3 +309,11 @@ def test_philox_known_answers_and_device_delay_replica():
     sparse = DeviceDelay("exp:mean=1:p=0.25:seed=5")
     hits = sum(1 for s in range(1, 801) if sparse.sample_ns(1, s) > 0)
     assert 150 < hits < 250
+    # the tails the straggler study sweeps: moments of the draws match the named distributions
+    n = 4000
+    ex = [DeviceDelay("exp:shift=0.5:mean=2:seed=3").sample_ns(0, s) / 1e6 for s in range(1, n + 1)]
+    assert min(ex) >= 0.5 and abs(sum(ex) / n - 2.5) < 0.15
+    ln = sorted(DeviceDelay("lognormal:mu=0.7:sigma=0.5:seed=4").sample_ns(2, s) / 1e6 for s in range(1, n + 1))
+    assert abs(ln[n // 2] - 2.0138) < 0.12                                  # median = e^mu
+    pa = sorted(DeviceDelay("pareto:xm=1.5:alpha=2:seed=6").sample_ns(1, s) / 1e6 for s in range(1, n + 1))
+    assert pa[0] >= 1.5 and abs(pa[n // 2] - 1.5 * 2 ** 0.5) < 0.1           # median = xm * 2^(1/alpha)
