@@ -66,9 +66,25 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_native_driver(force=False):
+    """build/distributed_nn_native: the stand-alone FC parameter-server program (counterpart of MPI_code's `make distributed`)."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    src = os.path.join(CSRC, "fc_ps_main.cpp")
+    out = os.path.join(ROOT, "build", "distributed_nn_native")
+    if force or _newer([src, LIB, os.path.join(ROOT, "include", "pdnn_b200.h")], out):
+        cmd = [nvcc] + NVCC_FLAGS + [src, "-o", out, "-L" + OUT_DIR, "-lpdnn_b200", "-Xlinker", "-rpath", "-Xlinker",
+                                    "$ORIGIN/../pytorch_distributed_nn_b200/lib"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("native driver build failed")
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
     print(build(a.force, a.verbose))
+    print(build_native_driver(a.force))

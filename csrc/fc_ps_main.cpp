@@ -33,12 +33,23 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--no-shortcircuit")) c.shortcircuit = 0;
         else if (!strcmp(a, "--timeline")) c.generate_timeline = 1;
         else if (!strcmp(a, "--host-protocol")) c.device_protocol = 0;
+        else if (!strcmp(a, "--help") || !strcmp(a, "-h")) {
+            printf("usage: %s [--workers 6] [--collect 2] [--iters 100] [--batch 128] [--lr 0.001] [--data DIR] [--out DIR]\n"
+                   "          [--delay-mask 0x7 --delay-us 500] [--no-shortcircuit] [--timeline] [--host-protocol] [--selftest]\n"
+                   "FC parameter server; the roles are threads of this process: master on GPU 0, --workers workers round-robin over the\n"
+                   "other visible GPUs (all on GPU 0 when there is only one), evaluator on the last GPU.\n"
+                   "--collect k: gradients the master waits for per layer; --delay-mask / --delay-us: injected per-layer delay of the\n"
+                   "workers in the mask; --host-protocol: host-thread transport instead of the device-flag protocol; --selftest: train\n"
+                   "a small net on one GPU and report the loss (MNIST idx files are read from --data, synthetic data otherwise).\n", argv[0]);
+            return 0;
+        }
         else if (!strcmp(a, "--selftest")) {
             float l0, l1;
             int rc = pdnn_fc_ps_selftest(60, &l0, &l1);
             printf("selftest rc=%d loss %.4f -> %.4f %s\n", rc, l0, l1, rc ? pdnn_last_error() : "");
             return rc;
         }
+        else { fprintf(stderr, "unknown argument %s (see --help)\n", a); return 2; }
     }
     pdnn_fc_ps_result_t r;
     int rc = pdnn_fc_ps_run(&c, &r);
