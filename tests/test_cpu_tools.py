@@ -111,3 +111,23 @@ def test_data_prepare_synthesizes_real_file_formats_once(tmp_path):
     xb, yb = b.train.next_batch(16)
     assert xa.shape == (16, 3, 32, 32) and (xa == xb).all() and (ya == yb).all()      # every rank reads the same files
     assert read_mnist(md).train.images.shape[1:] == (1, 28, 28)
+
+
+def test_native_fc_driver_builds_and_parses_its_flags():
+    """build/distributed_nn_native (counterpart of MPI_code's `make distributed`): links against the in-tree library,
+    documents its flags and refuses unknown ones. Running a job needs a GPU (tests/test_gpu_native_fc.py)."""
+    import importlib.util
+    import shutil
+    import pytest
+    if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+        pytest.skip("no nvcc")
+    spec = importlib.util.spec_from_file_location("pdnn_build", os.path.join(ROOT, "csrc", "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    if not os.path.exists(mod.LIB):
+        pytest.skip("libpdnn_b200.so not built")
+    exe = mod.build_native_driver()
+    r = subprocess.run([exe, "--help"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "--collect" in r.stdout and "--host-protocol" in r.stdout
+    r = subprocess.run([exe, "--no-such-flag"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 2 and "unknown argument" in r.stderr
