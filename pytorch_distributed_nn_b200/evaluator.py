@@ -199,3 +199,37 @@ def evaluate_checkpoints(train_dir, network_name, dataset, eval_interval_secs=5.
         if run_once or (max_polls is not None and polls >= max_polls):
             return results
         time.sleep(eval_interval_secs)
+
+
+def main(argv=None):
+    """``python -m pytorch_distributed_nn_b200.evaluator --checkpoint-dir DIR --network N --dataset D``: the stand-alone
+    evaluator process (flags of distributed_TF/src/nn_eval.py:36-45: checkpoint_dir, eval_interval_secs, run_once; eval_dir
+    becomes ``--out``, a JSON-lines file of (step, loss, precision@1) rows)."""
+    import argparse
+    import json
+    from .utils.data import read_cifar10, read_mnist
+    ap = argparse.ArgumentParser(description="poll a training directory and evaluate every new checkpoint")
+    ap.add_argument("--checkpoint-dir", "--train-dir", dest="checkpoint_dir", required=True)
+    ap.add_argument("--network", default="LeNet")
+    ap.add_argument("--dataset", default="MNIST", choices=["MNIST", "Cifar10"])
+    ap.add_argument("--data-dir", default=None)
+    ap.add_argument("--synthetic", action="store_true", help="random data of the dataset's shape (no files needed)")
+    ap.add_argument("--eval-interval-secs", type=float, default=1.0)
+    ap.add_argument("--run-once", action="store_true")
+    ap.add_argument("--max-polls", type=int, default=None)
+    ap.add_argument("--out", default="", help="append one JSON line per evaluated checkpoint")
+    a = ap.parse_args(argv)
+    if a.dataset == "MNIST":
+        data = read_mnist(a.data_dir or "MNIST_data", synthetic=a.synthetic).validation
+    else:
+        data = read_cifar10(a.data_dir or "cifar10_data", synthetic=a.synthetic).validation
+    rows = evaluate_checkpoints(a.checkpoint_dir, a.network, data, a.eval_interval_secs, a.run_once, a.max_polls)
+    if a.out:
+        with open(a.out, "a") as f:
+            for step, loss, prec in rows:
+                f.write(json.dumps({"step": step, "loss": loss, "precision_at_1": prec}) + "\n")
+    return rows
+
+
+if __name__ == "__main__":
+    main()

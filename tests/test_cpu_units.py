@@ -282,6 +282,16 @@ def test_polling_evaluator_restores_the_newest_checkpoint(tmp_path, capsys):
     assert "Precision @ 1" in capsys.readouterr().out
     # nothing new: a second poll evaluates nothing
     assert evaluate_checkpoints(str(tmp_path), "LeNet", data, eval_interval_secs=0.01, max_polls=2)[0][0] == 20
+    # the same thing as a process with nn_eval.py's flags
+    import json
+    import subprocess
+    import sys
+    out = tmp_path / "eval.jsonl"
+    r = subprocess.run([sys.executable, "-m", "pytorch_distributed_nn_b200.evaluator", "--checkpoint-dir", str(tmp_path), "--network", "LeNet",
+                        "--dataset", "MNIST", "--synthetic", "--run-once", "--out", str(out)], capture_output=True, text=True, timeout=300,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Precision @ 1" in r.stdout and json.loads(out.read_text().splitlines()[0])["step"] == 20
 
 
 def test_philox_known_answers_and_device_delay_replica():
