@@ -534,4 +534,7 @@ def build_network(name: str, batch: int, device="cuda", n_buckets: int = 8, exte
         return build_vgg(key, batch, device, n_buckets, external_w=external_w, external_g=external_g)
     if key in ("FC", "MLP"):
         return build_mlp([784, 500, 500, 800, 800, 200, 100, 100, 10], batch, device, min(n_buckets, 4), external_w=external_w, external_g=external_g)
+    if key == "FCDeep":
+        from ..models.mlp import DIMS_DEEP
+        return build_mlp(list(DIMS_DEEP), batch, device, min(n_buckets, 4), external_w=external_w, external_g=external_g)
     raise ValueError(f"unknown network {name!r}")

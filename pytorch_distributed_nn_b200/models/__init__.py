@@ -10,12 +10,13 @@ _PLAIN = {
     "LeNet": LeNet, "ResNet": ResNet18, "Resnet": ResNet18, "ResNet18": ResNet18, "ResNet34": ResNet34,
     "ResNet50": ResNet50, "ResNet101": ResNet101, "ResNet152": ResNet152,
     "VGG11": VGG11, "VGG13": VGG13, "VGG16": VGG16, "VGG19": VGG19, "FC": MLP, "MLP": MLP,
+    "FCDeep": lambda: MLP(DIMS_DEEP),          # the 28-layer net of pure_py_code/distributed_nn.py:41-96 and the TF study
 }
 _SPLIT = {
     "LeNet": LeNetSplit, "ResNet": ResNetSplit18, "Resnet": ResNetSplit18, "ResNet18": ResNetSplit18,
     "ResNet34": ResNetSplit34, "ResNet50": ResNetSplit50, "ResNet101": ResNetSplit101, "ResNet152": ResNetSplit152,
     "VGG11": lambda: VGGSplit("VGG11"), "VGG13": lambda: VGGSplit("VGG13"), "VGG16": lambda: VGGSplit("VGG16"),
-    "VGG19": lambda: VGGSplit("VGG19"), "FC": MLPSplit, "MLP": MLPSplit,
+    "VGG19": lambda: VGGSplit("VGG19"), "FC": MLPSplit, "MLP": MLPSplit, "FCDeep": lambda: MLPSplit(DIMS_DEEP),
 }
 
 
@@ -27,6 +28,6 @@ def build_model(name: str, split: bool = False):
 
 
 def input_shape(network: str, dataset: str = None):
-    if network in ("LeNet", "FC", "MLP") or (dataset or "").upper() == "MNIST":
+    if network in ("LeNet", "FC", "MLP", "FCDeep") or (dataset or "").upper() == "MNIST":
         return (1, 28, 28)
     return (3, 32, 32)

@@ -16,7 +16,7 @@ def add_fit_args(parser: argparse.ArgumentParser, distributed: bool = True) -> a
     g.add_argument("--seed", type=int, default=1, metavar="S", help="random seed (default: 1)")
     g.add_argument("--log-interval", type=int, default=10, metavar="N", help="steps between log lines")
     g.add_argument("--network", type=str, default="LeNet", metavar="N",
-                   help="LeNet | ResNet18 | ResNet34 | ResNet50 | ResNet101 | ResNet152 | VGG11 | VGG13 | VGG16 | VGG19 | FC")
+                   help="LeNet | ResNet18 | ResNet34 | ResNet50 | ResNet101 | ResNet152 | VGG11 | VGG13 | VGG16 | VGG19 | FC | FCDeep")
     g.add_argument("--dataset", type=str, default="MNIST", metavar="N", help="MNIST | Cifar10")
     if distributed:
         g.add_argument("--comm-type", type=str, default="Bcast", metavar="N", help="weight distribution: Bcast | Async")

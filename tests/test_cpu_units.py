@@ -108,7 +108,7 @@ def test_mnist_idx_reader_parses_big_endian_files(tmp_path):
     assert extract_labels(str(tmp_path / "lab"), 3).tolist() == [7, 1, 9]
 
 
-@pytest.mark.parametrize("name", ["LeNet", "ResNet18", "VGG11", "MLP"])
+@pytest.mark.parametrize("name", ["LeNet", "ResNet18", "VGG11", "MLP", "FCDeep"])
 def test_split_backward_equals_autograd_and_streams_in_reverse_order(name):
     from pytorch_distributed_nn_b200.models import build_model, input_shape
     torch.manual_seed(0)
@@ -175,7 +175,7 @@ def test_accuracy_and_flags():
 def test_engine_layout_matches_torch_parameter_order_on_meta_device():
     from pytorch_distributed_nn_b200.engine.network import build_network
     from pytorch_distributed_nn_b200.models import build_model
-    for name, count in (("LeNet", 8), ("ResNet18", 62), ("ResNet50", 161), ("VGG11", 34)):
+    for name, count in (("LeNet", 8), ("ResNet18", 62), ("ResNet50", 161), ("VGG11", 34), ("FC", 16), ("FCDeep", 56)):
         net = build_network(name, 128, device="meta")
         ref = build_model(name)
         assert [p.name for p in net.param_list] == [k for k, _ in ref.named_parameters()]
