@@ -131,3 +131,35 @@ def test_native_fc_driver_builds_and_parses_its_flags():
     assert r.returncode == 0 and "--collect" in r.stdout and "--host-protocol" in r.stdout
     r = subprocess.run([exe, "--no-such-flag"], capture_output=True, text=True, timeout=60)
     assert r.returncode == 2 and "unknown argument" in r.stderr
+
+
+def test_plot_study_reads_a_train_dir_and_a_sweep_file(tmp_path):
+    """tools/plot_study.py (analysis half of distributed_TF/tools/benchmark.py:60-263): the five figures' series and the
+    compute-time statistics (all samples / slowest worker per iteration) from the JSONL files a run leaves behind."""
+    import json
+    sys.path.insert(0, ROOT)
+    from tools import plot_study
+    run = tmp_path / "run"
+    run.mkdir()
+    with open(run / "master_rank0.jsonl", "w") as f:
+        for s in range(1, 11):
+            f.write(json.dumps({"step": s, "step_ms": 10.0 + s, "ts": 100.0 + s, "rank": 0}) + "\n")
+        f.write(json.dumps({"event": "summary", "steps": 10, "ts": 111.0}) + "\n")
+    for rank, slow in ((1, 1.0), (2, 3.0)):
+        with open(run / f"worker_rank{rank}.jsonl", "w") as f:
+            for s in range(1, 11):
+                f.write(json.dumps({"step": s, "loss": 2.3 / s, "total_s": 0.01 * slow * s, "ts": 100.0 + s - 0.5, "rank": rank}) + "\n")
+    with open(run / "time_loss_out_test", "w") as f:
+        f.write("5 5000.0 1.2 0.40\n10 10000.0 0.6 0.25\n")
+    study = tmp_path / "study.json"
+    study.write_text(json.dumps([{"name": "c1", "policy": "kofn", "k": 3, "interval_ms": 0.0, "inject_delay": "none", "images_per_sec": 1000.0,
+                                  "step_ms": {"p50": 1.0, "p99": 2.0}, "sets_per_step": 3.0}, {"name": "broken", "error": "x"}]))
+    rep = plot_study.main([f"a={run}", "--out", str(tmp_path / "figs"), "--study", str(study)])
+    st = rep["a"]["compute_times_ms"]
+    assert rep["a"]["steps"] == 10 and st["all"]["n"] == 20 and abs(st["all"]["max"] - 300.0) < 1e-6
+    assert abs(st["slowest_worker_per_iteration"]["p50"] - 150.0) < 1e-6          # worker 2 is always the slowest: 30 ms x step
+    assert [r["name"] for r in rep["study"]] == ["c1"]
+    assert len(rep["figures"]) == 5 and all(os.path.exists(p) for p in rep["figures"])
+    if rep["figures"][0].endswith(".csv"):
+        rows = open(os.path.join(tmp_path, "figs", "time_precision.csv")).read().splitlines()
+        assert rows[1:] == ["a,5,60", "a,10,75"]
