@@ -163,3 +163,42 @@ def test_plot_study_reads_a_train_dir_and_a_sweep_file(tmp_path):
     if rep["figures"][0].endswith(".csv"):
         rows = open(os.path.join(tmp_path, "figs", "time_precision.csv")).read().splitlines()
         assert rows[1:] == ["a,5,60", "a,10,75"]
+
+
+def test_chrome_trace_from_a_train_dir(tmp_path):
+    """tools/chrome_trace.py (the TF study's --timeline_logging, distributed_train.py:284-286): spans of the worker phases and of
+    the master's step / device timeline, one file for the run and one per step."""
+    import json
+    sys.path.insert(0, ROOT)
+    from tools import chrome_trace
+    run = tmp_path / "run"
+    run.mkdir()
+    with open(run / "master_rank0.jsonl", "w") as f:
+        for s in (1, 2):
+            f.write(json.dumps({"step": s, "step_ms": 8.0, "ts": 50.0 + 0.01 * s, "selected": [0, 1], "killed": [2],
+                                "device_timeline_us": {"wait_for_kth_arrival": 5000, "reduce_update_broadcast": 15, "bucket_ready_us": [1000, 3000, 5000]}}) + "\n")
+    with open(run / "worker_rank1.jsonl", "w") as f:
+        for s in (1, 2):
+            f.write(json.dumps({"step": s, "loss": 2.0, "killed": s == 2, "total_s": 0.007, "fetch_s": 0.001, "forward_s": 0.002, "backward_s": 0.004,
+                                "ts": 50.0 + 0.01 * s - 0.001}) + "\n")
+    files = chrome_trace.main([str(run), "-o", str(tmp_path / "trace.json"), "--per-step"])
+    ev = json.load(open(files[0]))["traceEvents"]
+    names = [e["name"] for e in ev]
+    assert names.count("step") == 2 and names.count("forward") == 2 and "backward + push (killed)" in names
+    assert sum(1 for n in names if n.startswith("bucket ")) == 6
+    step1 = [e for e in ev if e["ph"] == "X" and e["args"]["step"] == 1]
+    m = {e["name"]: e for e in step1}
+    # the tail ends where the step ends; the last bucket's instant sits at the end of the wait span
+    assert abs((m["reduce + update + broadcast tail"]["ts"] + 15) - (m["step"]["ts"] + m["step"]["dur"])) < 1e-3
+    w = m["wait for k-th arrival (last bucket)"]
+    last_bucket = [e for e in ev if e["name"] == "bucket 2 has k arrivals" and e["args"]["step"] == 1][0]
+    assert abs(last_bucket["ts"] - (w["ts"] + w["dur"])) < 1e-3
+    assert m["forward"]["ts"] == pytest_approx(m["fetch weights"]["ts"] + 1000.0)
+    assert len(files) == 3 and all(os.path.exists(p) for p in files)
+    per = json.load(open(files[1]))["traceEvents"]
+    assert {e["args"]["step"] for e in per if e["ph"] != "M"} == {1}
+
+
+def pytest_approx(v):
+    import pytest
+    return pytest.approx(v, abs=1e-2)
