@@ -184,6 +184,7 @@ class DistributedWorker(NN_Trainer):
 
         def on_log(i, loss):
             self.history.append({"step": i, "loss": loss})
+            self.logger.log(step=i, loss=loss)              # worker_rank<r>.jsonl, read by tools/plot_study.py / chrome_trace.py
             print("Worker: {}, Cur Step: {}, Train Loss: {:.4f}".format(self.rank, i, loss), flush=True)
             if ships_bn and i % eval_freq == 0:
                 import torch.distributed as dist
