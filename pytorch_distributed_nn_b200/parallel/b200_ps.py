@@ -336,9 +336,11 @@ class B200ParameterServer:
 
     def enable_cuda_graph(self, x_example=None, y_example=None):
         """Capture one complete step of this rank into CUDA graphs: the worker's step (wait -> fetch weights -> forward ->
-        loss -> backward with bucket pushes) as one graph replayed on the caller's stream and, on rank 0, the master's
-        kernels as a second graph replayed on the master's stream (two linear chains; a forked single graph measured
-        0.8 ms slower per ResNet-18 step). Later ``train_step`` calls copy the batch into static buffers and replay. The
+        loss -> backward with bucket pushes) as one graph replayed on the caller's stream. On rank 0 the master's kernels
+        are part of that graph in *gated* mode (each bucket's {wait, reduce} pair forks to the master's stream behind
+        this rank's own push of the bucket and joins at the end of the step) and a second graph replayed on the master's
+        stream in *free* mode (k < n, interval policy, master-only rank 0: the master must not wait for worker 0).
+        Later ``train_step`` calls copy the batch into static buffers and replay. The
         step number moves to device words (`pdnn_ps_wait_next`, `pdnn_ps_push_dev`, master ``step_ptr``) so nothing in the
         captured launches depends on it. Call on EVERY rank at the same step (one real step runs as warm-up).
         Host-computed per-step delays (``delay_fn``) cannot be replayed and are rejected; device-sampled delays
@@ -388,9 +390,9 @@ class B200ParameterServer:
         return self.arena.tensor(self.off_slots[w], self.net.total * self.slot_elem, dt)
 
     def _step_body(self, x, y):
-        """Worker kernels first, master kernels second in HOST order (on the device they run side by side): nothing the
-        worker's enqueue may do on the host (a first-use allocation, a lazily created buffer) then happens while a master
-        kernel that spins on a flag is already resident."""
+        """Worker kernels first, master kernels second in HOST order (on the device they run side by side): the first
+        launch of a kernel loads its module lazily and that load can wait for the context to drain, which never happens
+        while a master kernel that spins on a flag is already resident ("Lazy kernel loading")."""
         loss = None
         if self.is_worker:
             loss = self._worker_part(x, y)
