@@ -246,6 +246,9 @@ class PinnedBatchStager:
             sx, sy = x.reshape(self.hx[b].shape), y
             self._src[b] = (sx, sy)                          # keep the source alive until the copy has run
         else:
+            # the host may be several steps ahead of the device: the DMA that last read this pinned buffer must have run
+            # before the buffer is overwritten (an event that was never recorded returns at once)
+            self.ready[b].synchronize()
             self.hx[b].view(-1).copy_(x.reshape(-1))         # same element count, any host layout ([B,1,28,28] for a [B,784] net)
             self.hy[b].copy_(y)
             sx, sy = self.hx[b], self.hy[b]
