@@ -37,14 +37,6 @@ class DataSet:
 
     def _shuffle(self):
         perm = self._rng.permutation(self._num_examples)
-        if getattr(self, "_pinned", None) is not None:
-            # page-locked arrays (``_NextBatchDataset.pin_memory``) are permuted IN PLACE so that they stay page-locked and
-            # later batches are still DMA'd from where they are; batches handed out earlier may still be on their way
-            # to the device, hence the synchronisation (once per epoch)
-            torch.cuda.synchronize()
-            self._images[:] = self._images[perm]
-            self._labels[:] = self._labels[perm]
-            return
         self._images = self._images[perm]
         self._labels = self._labels[perm]
 
@@ -187,8 +179,8 @@ class _NextBatchDataset(torch.utils.data.Dataset):
 
     def pin_memory(self):
         """Page-lock the image / label arrays once (device backend): ``next_batch`` then hands out views of pinned memory
-        and the input staging copies them to the GPU without an intermediate host copy. The reshuffle at the end of an
-        epoch permutes the page-locked arrays in place (``DataSet._shuffle``), so this holds for every epoch."""
+        and the input staging copies them to the GPU without an intermediate host copy. After an epoch's reshuffle the
+        arrays are new (pageable) ones and staging falls back to its own pinned buffers."""
         ds = self.dataset
         if not torch.cuda.is_available() or getattr(ds, "_pinned", None) is not None:
             return self

@@ -327,26 +327,3 @@ def test_philox_known_answers_and_device_delay_replica():
     assert abs(ln[n // 2] - 2.0138) < 0.12                                  # median = e^mu
     pa = sorted(DeviceDelay("pareto:xm=1.5:alpha=2:seed=6").sample_ns(1, s) / 1e6 for s in range(1, n + 1))
     assert pa[0] >= 1.5 and abs(pa[n // 2] - 1.5 * 2 ** 0.5) < 0.1           # median = xm * 2^(1/alpha)
-
-
-def test_pinned_dataset_is_reshuffled_in_place(monkeypatch):
-    """A page-locked data set (device backend) must stay page-locked across epochs: the reshuffle permutes the arrays in
-    place -- after waiting for the device, because earlier batches may still be in flight -- instead of replacing them."""
-    from pytorch_distributed_nn_b200.utils.data import DataSet
-    x = np.arange(40, dtype=np.float32).reshape(10, 4)
-    y = np.arange(10, dtype=np.int64)
-    ds = DataSet(x.copy(), y.copy(), seed=3)
-    timgs, tlabs = torch.from_numpy(np.ascontiguousarray(ds._images)), torch.from_numpy(np.ascontiguousarray(ds._labels))
-    ds._pinned = (timgs, tlabs)                       # what _NextBatchDataset.pin_memory() sets up (without the page-locking)
-    ds._images, ds._labels = timgs.numpy(), tlabs.numpy()
-    synced = []
-    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: synced.append(1))
-    addr = ds._images.ctypes.data
-    seen = []
-    for _ in range(4):                                # 10 examples, batches of 4: the third call wraps into a new epoch
-        bx, by = ds.next_batch(4)
-        assert np.array_equal(bx[:, 0] / 4, by.astype(np.float32))          # rows and labels stay paired
-        seen.append(by.copy())
-    assert ds.epochs_completed == 1 and len(synced) == 1
-    assert ds._images.ctypes.data == addr and timgs.data_ptr() == addr       # same memory, permuted in place
-    assert sorted(ds._labels.tolist()) == list(range(10))
