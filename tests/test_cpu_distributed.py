@@ -145,3 +145,53 @@ def test_ddp_comparator_two_ranks_average_the_bucketed_gradients():
     for rc, o in outs:
         assert rc == 0, o[-2000:]
         assert "DDP_OK" in o
+
+
+def test_resume_continues_weights_step_number_and_momentum(tmp_path):
+    """``--resume model_step_<n>`` on the message backend: the job continues at step n+1 from the checkpointed weights AND the
+    momentum of its sidecar (TF Supervisor restores everything, distributed_train.py:215-223). Checked against a
+    single-process replay in which the two workers' data streams start again (they do: workers are new processes) and the
+    momentum is carried over; a replay that starts the momentum at zero must NOT match."""
+    lr, mu = 0.05, 0.9
+    common = ["--straggler-policy", "all", "--lr", str(lr), "--momentum", str(mu), "--grad-dtype", "fp32", "--comm-type", "Bcast"]
+    a, b = tmp_path / "a", tmp_path / "b"
+    _run(["--max-steps", "2", "--eval-freq", "2"] + common, a)
+    from pytorch_distributed_nn_b200.utils import checkpoint as ckpt
+    first = ckpt.latest_checkpoint(str(a))
+    assert first is not None and first[1] == 2
+    _run(["--max-steps", "4", "--eval-freq", "4", "--resume", first[0]] + common, b)
+    sd, step, _ = ckpt.load_checkpoint(ckpt.latest_checkpoint(str(b))[0])
+    assert step == 4
+    assert [r["step"] for r in _master_log(b)] == [3, 4]
+    from pytorch_distributed_nn_b200 import mnist
+    from pytorch_distributed_nn_b200.models import build_model
+
+    def replay(carry_momentum):
+        torch.manual_seed(1)
+        net = build_model("LeNet", split=True)
+        params = list(net.parameters())
+        mom = [torch.zeros_like(p) for p in params]
+        for leg in range(2):                                # two jobs of two steps; each job's workers read their data from the start
+            data = [mnist.read_data_sets("MNIST_data", reshape=True, synthetic=True, worker_id=r, n_workers=3).train for r in (1, 2)]
+            if leg == 1 and not carry_momentum:
+                mom = [torch.zeros_like(p) for p in params]
+            for _ in range(2):
+                gsum = [torch.zeros_like(p) for p in params]
+                for d in data:
+                    x, y = d.next_batch(16)
+                    net.zero_grad()
+                    out = net(torch.from_numpy(x).float())
+                    torch.nn.functional.cross_entropy(out, torch.from_numpy(y)).backward()
+                    net.backward(out.grad, None, [])
+                    for g, p in zip(gsum, params):
+                        g += p.grad
+                with torch.no_grad():
+                    for p, g, m in zip(params, gsum, mom):
+                        m.mul_(mu).add_(g / 2)
+                        p.add_(m, alpha=-lr)
+        return {k: p.detach().clone() for (k, _), p in zip(net.named_parameters(), params)}
+
+    good, bad = replay(True), replay(False)
+    for k in good:
+        assert torch.allclose(sd[k], good[k], rtol=1e-5, atol=1e-6), k
+    assert any(not torch.allclose(sd[k], bad[k], rtol=1e-3, atol=1e-4) for k in bad)
